@@ -1,0 +1,143 @@
+"""ctypes binding of libcollision_b200.so (the C ABI of include/collision_b200.h).
+
+There is NO fallback path: if the library is missing or a call fails, this
+module raises.  torch is used for device memory, streams and events only.
+"""
+import ctypes as C
+from pathlib import Path
+
+import numpy as np
+import torch
+
+_HERE = Path(__file__).resolve().parent
+_LIB_PATH = _HERE / "libcollision_b200.so"
+_lib = None
+
+COL_F32, COL_F64 = 0, 1
+
+_vp, _u64, _u32, _int, _sz = C.c_void_p, C.c_uint64, C.c_uint32, C.c_int, C.c_size_t
+
+# name -> (restype, argtypes); mirrors include/collision_b200.h one to one
+SIGNATURES = {
+    "col_abi_version": (_int, []),
+    "col_built_arch": (_int, []),
+    "col_reduce_scratch_bytes": (_sz, []),
+    "col_bounds": (_int, [_vp, _u64, _int, _u32, _vp, _vp, _vp]),
+    "col_sum": (_int, [_vp, _u64, _int, _u32, _vp, _vp, _vp]),
+    "col_morton": (_int, [_vp, _vp, _vp, _vp, _int, _u32, _u32, _vp]),
+    "col_scan_scratch_bytes": (_sz, [_u64]),
+    "col_exclusive_scan_u32": (_int, [_vp, _u64, _vp, _vp, _vp]),
+    "col_sort_scratch_bytes": (_sz, [_u64, _u32, _u32]),
+    "col_sort_pairs": (_int, [_vp, _vp, _vp, _vp, _u64, _u32, _u32, _u32, _vp, _vp]),
+    "col_radix_pass": (_int, [_vp, _vp, _vp, _vp, _u64, _u32, _u32, _u32, _u32, _vp, _vp]),
+    "col_build_tree": (_int, [_vp, _vp, _vp, _u32, _vp]),
+    "col_fill_leaves": (_int, [_vp, _vp, _u32, _vp]),
+    "col_refit": (_int, [_vp, _vp, _vp, _vp, _vp, _int, _u32, _vp]),
+    "col_leaf_bounds": (_int, [_vp, _vp, _vp, _vp, _int, _u32, _vp]),
+    "col_traverse_count": (_int, [_vp, _vp, _vp, _int, _u32, _u32, _u32, _vp]),
+    "col_traverse_write": (_int, [_vp, _u64, _vp, _u64, _vp, _vp, _int, _u32, _u32, _u32, _vp]),
+    "col_traverse_atomic": (_int, [_vp, _vp, _u32, _vp, _vp, _int, _u32, _u32, _u32, _vp]),
+    "col_find_offsets": (_int, [_vp, _u64, _u32, _vp, _u64, _u32, _vp]),
+    "col_gather": (_int, [_vp, _vp, _vp, _u64, _u32, _u32, _vp]),
+    "col_scatter": (_int, [_vp, _vp, _vp, _u64, _u32, _u32, _vp]),
+    "col_fill_u32": (_int, [_vp, _u32, _u64, _vp]),
+    "col_range": (_int, [_vp, _u64, _vp]),
+    "col_copy": (_int, [_vp, _vp, _u64, _vp]),
+}
+
+
+class CollisionLibraryError(RuntimeError):
+    pass
+
+
+def lib_path():
+    return _LIB_PATH
+
+
+def lib():
+    """The loaded library.  Raises (never falls back) when it has not been built."""
+    global _lib
+    if _lib is None:
+        if not _LIB_PATH.exists():
+            raise CollisionLibraryError(
+                "{} not found: build it with `python -m collision_b200.build` "
+                "(nvcc, sm_100a).  collision_b200 has no CPU or PyTorch fallback.".format(_LIB_PATH))
+        handle = C.CDLL(str(_LIB_PATH))
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(handle, name)   # AttributeError if the ABI is incomplete
+            fn.restype, fn.argtypes = res, args
+        _lib = handle
+    return _lib
+
+
+def check(rc, what):
+    if rc == 0:
+        return
+    if rc > 0:
+        raise CollisionLibraryError("{}: CUDA error {} ({})".format(what, rc, _cuda_error_name(rc)))
+    raise CollisionLibraryError("{}: {}".format(what, {-1: "bad argument", -2: "size too large",
+                                                     -3: "unsupported dtype"}.get(rc, rc)))
+
+
+def _cuda_error_name(rc):
+    try:
+        rt = C.CDLL("libcudart.so")
+        rt.cudaGetErrorName.restype = C.c_char_p
+        return rt.cudaGetErrorName(C.c_int(rc)).decode()
+    except Exception:
+        return "?"
+
+
+# ------------------------------------------------------------ torch helpers
+def ptr(t):
+    """Device pointer of a tensor (None -> NULL)."""
+    if t is None:
+        return None
+    if not isinstance(t, torch.Tensor):
+        raise TypeError("expected a torch.Tensor device buffer, got {}".format(type(t)))
+    if not t.is_cuda:
+        raise ValueError("buffer must live on a CUDA device")
+    if not t.is_contiguous():
+        raise ValueError("buffer must be contiguous")
+    return t.data_ptr()
+
+
+def stream_ptr(cq):
+    return cq.cuda_stream
+
+
+def begin(cq, wait_for):
+    """Make `cq` wait for the given events (the reference's wait_for lists)."""
+    for e in wait_for or ():
+        if e is not None:
+            cq.wait_event(e)
+
+
+def done(cq):
+    """Event marking everything enqueued on `cq` so far (the reference returns cl.Event)."""
+    ev = torch.cuda.Event()
+    ev.record(cq)
+    return ev
+
+
+def device_of(ctx):
+    dev = torch.device(ctx)
+    if dev.type != "cuda":
+        raise ValueError("collision_b200 runs on CUDA devices only (got {})".format(dev))
+    if dev.index is None:
+        dev = torch.device("cuda", torch.cuda.current_device())
+    return dev
+
+
+def alloc_bytes(ctx, nbytes):
+    """Private scratch (the reference's HOST_NO_ACCESS cl.Buffer)."""
+    return torch.empty(max(int(nbytes), 1), dtype=torch.uint8, device=ctx)
+
+
+def float_code(dt):
+    dt = np.dtype(dt).base
+    if dt == np.float32:
+        return COL_F32
+    if dt == np.float64:
+        return COL_F64
+    raise ValueError("Invalid dtype: {}".format(dt))

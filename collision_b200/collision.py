@@ -1,0 +1,207 @@
+"""LBVH sphere-collision pipeline (mirror of collision/collision.py upstream).
+
+Collider keeps the reference's constructor, `resize`, `n_nodes`, `padded_size`
+and `get_collisions(cq, coords_buf, radii_buf, n_collisions_buf, collisions_buf,
+n_collisions, wait_for)`; Node / NO_NODE and the 16-byte Node, 32/64-byte Bound
+and 4-lane coordinate layouts are unchanged.  Handles map as
+ctx -> torch.device('cuda:i'), cq -> torch.cuda.Stream, cl.Buffer -> torch.Tensor,
+cl.Event -> torch.cuda.Event.
+
+Stages (all hand-written sm_100a kernels behind include/collision_b200.h):
+  scene bounds (one launch)        <- bounds1 + bounds2           collision.py:157-159
+  Morton codes + ids (one launch)  <- fill + range + calculateCodes        :138-165
+  one-sweep stable sort            <- RadixSorter.sort, 8 x (5..9 launches) :167-169
+  Karras tree (one launch)         <- fillInternal + generateBVH           :171-180
+  leaf boxes + refit (one launch)  <- leafBounds + internalBounds          :181-190
+  traversal                        <- traverse                              :191-196
+Traversal commits pairs either in the deterministic order of the reference's
+work-items run sequentially (count -> scan -> write; the default) or through one
+atomic counter in arbitrary order exactly like upstream (`ordered=False`).
+"""
+import torch
+from numpy import dtype, iinfo
+
+from . import _lib
+from .bounds import Bounds
+from .misc import Program, roundUp, same_context
+from .misc import np_float_dtypes as _float_names
+from .radix import RadixSorter
+
+np_float_dtypes = set(map(dtype, _float_names))
+
+Node = dtype([('parent', 'uint32'), ('right_edge', 'uint32'), ('data', 'uint32', 2)])
+
+NO_NODE = iinfo(Node.fields['parent'][0]).max
+
+MORTON_BITS = 30   # 3 x 10 bits (collision.cl:23)
+
+
+class CollisionProgram(Program):
+    """collision/collision.py:13-29.  `kernels` exposes the reference's kernel names
+    with their argument lists -- (cq, global_size, local_size, *args, wait_for=None)
+    -- because upstream's tests launch them directly (tests/test_collision.py)."""
+
+    def __init__(self, ctx, coord_dtype=dtype('float32')):
+        coord_dtype = dtype(coord_dtype)
+        if coord_dtype not in np_float_dtypes:
+            raise ValueError("Invalid dtype: {}".format(coord_dtype))
+        if coord_dtype == dtype('float16'):
+            raise ValueError("Unsupported dtype: float16 (float32 / float64)")
+        self.coord_dtype = coord_dtype
+        super().__init__(ctx)
+        self._code = _lib.float_code(coord_dtype)
+        L = _lib.lib()
+        code = self._code
+
+        def kernel(fn):
+            def launch(cq, global_size, local_size, *args, wait_for=None):
+                _lib.begin(cq, wait_for)
+                fn(cq, *args)
+                return _lib.done(cq)
+            return launch
+
+        def _range(cq, global_size, local_size, idxs, wait_for=None):
+            _lib.begin(cq, wait_for)
+            _lib.check(L.col_range(_lib.ptr(idxs), int(global_size[0]), _lib.stream_ptr(cq)), "col_range")
+            return _lib.done(cq)
+
+        def calc_codes(cq, codes, coords, rng, n):
+            _lib.check(L.col_morton(_lib.ptr(codes), None, _lib.ptr(coords), _lib.ptr(rng), code, n, n,
+                                    _lib.stream_ptr(cq)), "col_morton")
+
+        def fill_internal(cq, nodes, ids, n):
+            _lib.check(L.col_fill_leaves(_lib.ptr(nodes), _lib.ptr(ids), n, _lib.stream_ptr(cq)), "col_fill_leaves")
+
+        def generate_bvh(cq, codes, nodes, n):
+            _lib.check(L.col_build_tree(_lib.ptr(codes), None, _lib.ptr(nodes), n, _lib.stream_ptr(cq)),
+                       "col_build_tree")
+
+        def leaf_bounds(cq, bounds, coords, radii, nodes, n):
+            _lib.check(L.col_leaf_bounds(_lib.ptr(bounds), _lib.ptr(coords), _lib.ptr(radii), _lib.ptr(nodes),
+                                         code, n, _lib.stream_ptr(cq)), "col_leaf_bounds")
+
+        def internal_bounds(cq, bounds, flags, nodes, n):
+            _lib.check(L.col_refit(_lib.ptr(bounds), _lib.ptr(flags), _lib.ptr(nodes), None, None, code, n,
+                                   _lib.stream_ptr(cq)), "col_refit")
+
+        def traverse(cq, collisions, nxt, n_collisions, nodes, bounds, n):
+            _lib.check(L.col_traverse_atomic(_lib.ptr(collisions), _lib.ptr(nxt), n_collisions, _lib.ptr(nodes),
+                                             _lib.ptr(bounds), code, n, 0, n, _lib.stream_ptr(cq)),
+                       "col_traverse_atomic")
+
+        self.kernels = {
+            'range': _range,
+            'calculateCodes': kernel(calc_codes),
+            'fillInternal': kernel(fill_internal),
+            'generateBVH': kernel(generate_bvh),
+            'leafBounds': kernel(leaf_bounds),
+            'internalBounds': kernel(internal_bounds),
+            'traverse': kernel(traverse),
+        }
+
+
+class Collider:
+    code_dtype = dtype('uint32')
+    flag_dtype = dtype('uint32')
+    counter_dtype = dtype('uint32')
+    id_dtype = dtype('uint32')
+
+    def __init__(self, ctx, size, ngroups, group_size, coord_dtype=dtype('float32'),
+                 program=None, sorter_programs=(None, None), reducer_program=None, ordered=True):
+        coord_dtype = dtype(coord_dtype)
+        self.size = size
+        self.group_size = group_size
+        self.ordered = ordered
+
+        self.sorter = RadixSorter(
+            ctx, self.padded_size, group_size,
+            key_dtype=self.code_dtype, value_dtype=self.id_dtype,
+            program=sorter_programs[0], scan_program=sorter_programs[1])
+        self.reducer = Bounds(ctx, ngroups, group_size, coord_dtype=dtype((coord_dtype, 3)),
+                              program=reducer_program)
+        if program is None:
+            program = CollisionProgram(ctx, coord_dtype)
+        else:
+            if not same_context(program.context, ctx):
+                raise ValueError("Collider and program context must match")
+            if program.coord_dtype != coord_dtype:
+                raise ValueError("Collider and program coord_dtype must match")
+        self.program = program
+        self._bufs_for = None   # device scratch is allocated on first use
+
+    # -- scratch ----------------------------------------------------------
+    def _ensure_scratch(self):
+        key = (self.size, self.padded_size)
+        if self._bufs_for == key:
+            return
+        ctx = self.program.context
+        L = _lib.lib()
+        # can't sort in place (collision.py:60-69)
+        self._ids_bufs = [_lib.alloc_bytes(ctx, self.padded_size * 4) for _ in range(2)]
+        self._codes_bufs = [_lib.alloc_bytes(ctx, self.padded_size * 4) for _ in range(2)]
+        self._nodes_buf = _lib.alloc_bytes(ctx, self.n_nodes * Node.itemsize)
+        # dual use: scene bounds first, per-node boxes afterwards (collision.py:74-78)
+        self._bounds_buf = _lib.alloc_bytes(ctx, max(self.n_nodes, 2) * 2 * 4 * self.program.coord_dtype.itemsize)
+        self._flags_buf = _lib.alloc_bytes(ctx, self.n_nodes * 4)
+        self._counts_buf = _lib.alloc_bytes(ctx, self.size * 4)
+        self._scan_scratch = _lib.alloc_bytes(ctx, L.col_scan_scratch_bytes(self.size))
+        self._total_buf = torch.zeros(1, dtype=torch.int64, device=ctx)
+        self._bufs_for = key
+
+    def resize(self, size=None, ngroups=None, group_size=None, radix_bits=None):
+        if size is not None:
+            self.size = size
+        if group_size is not None:
+            self.group_size = group_size
+        # upstream passes roundUp(size, group_size) here (collision.py:94); the
+        # sorter needs a multiple of 2 * group_size, which is what padded_size is
+        self.sorter.resize(self.padded_size, group_size, radix_bits)
+        self.reducer.resize(ngroups, group_size)
+
+    @property
+    def n_nodes(self):
+        return self.size * 2 - 1
+
+    @property
+    def padded_size(self):
+        return roundUp(self.size, 2 * self.group_size)
+
+    # -- the hot path -----------------------------------------------------
+    def get_collisions(self, cq, coords_buf, radii_buf, n_collisions_buf, collisions_buf,
+                       n_collisions, wait_for=None):
+        if collisions_buf is None and n_collisions > 0:
+            raise ValueError("Invalid collisions_buf for n_collisions > 0")
+        L, P, S = _lib.lib(), _lib.ptr, _lib.stream_ptr(cq)
+        n, code = self.size, self.program._code
+        self._ensure_scratch()
+        _lib.begin(cq, wait_for)
+
+        _lib.check(L.col_bounds(P(coords_buf), n, code, 4, P(self._bounds_buf), P(self.reducer._ensure_scratch()), S),
+                   "col_bounds")
+        _lib.check(L.col_morton(P(self._codes_bufs[0]), P(self._ids_bufs[0]), P(coords_buf), P(self._bounds_buf),
+                                code, n, self.padded_size, S), "col_morton")
+        # padding keys are not needed by this sort: only the n real keys move
+        _lib.check(L.col_sort_pairs(P(self._codes_bufs[0]), P(self._codes_bufs[1]), P(self._ids_bufs[0]),
+                                    P(self._ids_bufs[1]), n, 4, 4, MORTON_BITS, P(self.sorter._ensure_scratch()), S),
+                   "col_sort_pairs")
+        _lib.check(L.col_build_tree(P(self._codes_bufs[1]), P(self._ids_bufs[1]), P(self._nodes_buf), n, S),
+                   "col_build_tree")
+        _lib.check(L.col_refit(P(self._bounds_buf), P(self._flags_buf), P(self._nodes_buf), P(coords_buf),
+                               P(radii_buf), code, n, S), "col_refit")
+        if self.ordered:
+            _lib.check(L.col_traverse_count(P(self._counts_buf), P(self._nodes_buf), P(self._bounds_buf), code,
+                                            n, 0, n, S), "col_traverse_count")
+            _lib.check(L.col_exclusive_scan_u32(P(self._counts_buf), n, P(self._total_buf),
+                                                P(self._scan_scratch), S), "col_exclusive_scan_u32")
+            # counter = true total (low 32 bits, as upstream's uint counter)
+            _lib.check(L.col_copy(P(n_collisions_buf), P(self._total_buf), 4, S), "col_copy")
+            if n_collisions > 0:
+                _lib.check(L.col_traverse_write(P(collisions_buf), n_collisions, P(self._counts_buf), 0,
+                                                P(self._nodes_buf), P(self._bounds_buf), code, n, 0, n, S),
+                           "col_traverse_write")
+        else:
+            _lib.check(L.col_fill_u32(P(n_collisions_buf), 0, 1, S), "col_fill_u32")
+            _lib.check(L.col_traverse_atomic(P(collisions_buf), P(n_collisions_buf), n_collisions,
+                                             P(self._nodes_buf), P(self._bounds_buf), code, n, 0, n, S),
+                       "col_traverse_atomic")
+        return _lib.done(cq)

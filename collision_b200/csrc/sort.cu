@@ -1,0 +1,374 @@
+// sort.cu -- stable LSD radix sort, one-sweep with decoupled look-back.
+//
+// Replaces RadixSorter.sort (collision/radix.py:118-170).  The reference runs,
+// for each 4-bit digit, block_sort (in-place local-memory sort by successive
+// 1-bit splits + digit-major histogram, collision/radix.cl:48-102), a
+// multi-launch prefix scan of that histogram, scatter (radix.cl:104-139) and two
+// full-array copies back -- ~384 B moved per (key, value).  Here:
+//
+//   1. ONE histogram kernel reads the keys once and counts every 8-bit digit of
+//      every pass into shared-memory histograms (4 x 256 bins for u32 keys).
+//   2. A one-block kernel turns the histograms into exclusive digit bases.
+//   3. ONE kernel per pass: a tile of keys is loaded warp-striped, ranked inside
+//      its warp with match.any (stable: lane order within a row, rows in
+//      order), combined across warps through per-warp digit counters in shared
+//      memory, the tile's 256 digit counts are chained to the preceding tiles by
+//      decoupled look-back on 32-bit {flag:2, count:30} words, and the tile is
+//      written out through shared memory in digit order so that global stores
+//      are runs of consecutive addresses.
+//
+// Traffic: 4n + passes * 2 * (key + value) * n bytes -> 68 B per (u32, u32)
+// pair, 36 B per u32 key: the HBM roofline of the op.  Stability is part of
+// the contract (the sorted position is the leaf index of the tree).
+#include "common.cuh"
+
+namespace {
+
+constexpr int RADIX_BITS = 8;
+constexpr int RADIX = 1 << RADIX_BITS;
+constexpr int MAX_PASSES = 8;
+
+constexpr int SORT_THREADS = 512;
+constexpr int SORT_WARPS = SORT_THREADS / 32;
+
+constexpr uint32_t ST_PARTIAL = 1u << 30;
+constexpr uint32_t ST_INCLUSIVE = 2u << 30;
+constexpr uint32_t ST_VALUE = (1u << 30) - 1;
+
+template <typename K> struct Tile { static constexpr int ITEMS = 16; };
+template <> struct Tile<uint64_t> { static constexpr int ITEMS = 8; };
+
+// ---------------------------------------------------------------- histogram
+constexpr int HIST_THREADS = 512;
+constexpr int HIST_ITEMS = 16;  // keys per thread per iteration
+
+template <typename K>
+__global__ void __launch_bounds__(HIST_THREADS)
+histogram_kernel(const K* __restrict__ keys, uint64_t n, uint32_t* __restrict__ ghist, uint32_t shift0,
+                 uint32_t bits, uint32_t npass) {
+    __shared__ uint32_t sh[MAX_PASSES * RADIX];
+    for (int i = threadIdx.x; i < MAX_PASSES * RADIX; i += HIST_THREADS) sh[i] = 0;
+    __syncthreads();
+    const uint32_t mask = (1u << bits) - 1;
+    const uint64_t chunk = (uint64_t)HIST_THREADS * HIST_ITEMS;
+    for (uint64_t base = (uint64_t)blockIdx.x * chunk; base < n; base += (uint64_t)gridDim.x * chunk) {
+        K k[HIST_ITEMS];
+#pragma unroll
+        for (int i = 0; i < HIST_ITEMS; i++) {
+            const uint64_t e = base + (uint64_t)i * HIST_THREADS + threadIdx.x;
+            k[i] = e < n ? keys[e] : (K)0;
+        }
+#pragma unroll
+        for (int i = 0; i < HIST_ITEMS; i++) {
+            const uint64_t e = base + (uint64_t)i * HIST_THREADS + threadIdx.x;
+            if (e < n)
+                for (uint32_t p = 0; p < npass; p++)
+                    atomicAdd(&sh[p * RADIX + (uint32_t)((k[i] >> (shift0 + p * bits)) & mask)], 1u);
+        }
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < (int)npass * RADIX; i += HIST_THREADS)
+        if (sh[i]) atomicAdd(&ghist[i], sh[i]);
+}
+
+// exclusive scan of each pass's 256 bins, in place (one warp-shuffle block scan per pass)
+__global__ void __launch_bounds__(RADIX) digit_base_kernel(uint32_t* ghist) {
+    __shared__ uint32_t warp_tot[RADIX / 32];
+    uint32_t* h = ghist + blockIdx.x * RADIX;
+    const uint32_t c = h[threadIdx.x];
+    uint32_t inc = c;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t up = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane_id() >= o) inc += up;
+    }
+    if (lane_id() == 31) warp_tot[threadIdx.x >> 5] = inc;
+    __syncthreads();
+    uint32_t base = 0;
+    for (int w = 0; w < (int)(threadIdx.x >> 5); w++) base += warp_tot[w];
+    h[threadIdx.x] = base + inc - c;
+}
+
+// ----------------------------------------------------------------- onesweep
+template <typename K, bool HAS_VALUES>
+__global__ void __launch_bounds__(SORT_THREADS, 2)
+onesweep_kernel(const K* __restrict__ keys_in, K* __restrict__ keys_out, const uint32_t* __restrict__ vals_in,
+                uint32_t* __restrict__ vals_out, uint32_t n, const uint32_t* __restrict__ digit_base,
+                uint32_t* __restrict__ status, unsigned* ticket, uint32_t shift, uint32_t mask) {
+    constexpr int ITEMS = Tile<K>::ITEMS;
+    constexpr int TILE = SORT_THREADS * ITEMS;
+    constexpr int WARP_ITEMS = 32 * ITEMS;
+
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    K* s_keys = reinterpret_cast<K*>(smem_raw);                                     // TILE keys
+    uint32_t* s_whist = reinterpret_cast<uint32_t*>(smem_raw + sizeof(K) * TILE);   // SORT_WARPS x RADIX
+    uint32_t* s_vals = s_whist + SORT_WARPS * RADIX;                                // TILE values (if any)
+    __shared__ uint32_t s_digit_start[RADIX];
+    __shared__ uint32_t s_global_off[RADIX];
+    __shared__ uint32_t s_scan_warp[RADIX / 32];
+    __shared__ unsigned s_tile;
+
+    if (threadIdx.x == 0) s_tile = atomicAdd(ticket, 1u);
+    for (int i = threadIdx.x; i < SORT_WARPS * RADIX; i += SORT_THREADS) s_whist[i] = 0;
+    __syncthreads();
+    const unsigned tile = s_tile;
+    const uint32_t tile_base = tile * (uint32_t)TILE;
+    const uint32_t valid = min((uint32_t)TILE, n - tile_base);
+    const unsigned warp = threadIdx.x >> 5, lane = lane_id();
+    const uint32_t warp_off = warp * WARP_ITEMS;
+
+    // ---- load (warp-striped: row i of a warp is 32 consecutive keys)
+    K key[ITEMS];
+#pragma unroll
+    for (int i = 0; i < ITEMS; i++) {
+        const uint32_t e = warp_off + i * 32 + lane;
+        key[i] = e < valid ? keys_in[tile_base + e] : (K)~(K)0;  // padding sorts last within the tile
+    }
+    uint32_t val[HAS_VALUES ? ITEMS : 1];
+    if (HAS_VALUES) {
+#pragma unroll
+        for (int i = 0; i < ITEMS; i++) {
+            const uint32_t e = warp_off + i * 32 + lane;
+            val[i] = e < valid ? vals_in[tile_base + e] : 0u;
+        }
+    }
+
+    // ---- rank inside the warp (stable)
+    uint32_t* my_hist = s_whist + warp * RADIX;
+    uint16_t rank[ITEMS];
+    const unsigned lt = lanemask_lt();
+#pragma unroll
+    for (int i = 0; i < ITEMS; i++) {
+        const uint32_t d = (uint32_t)(key[i] >> shift) & mask;
+        const unsigned peers = __match_any_sync(0xffffffffu, d);
+        const int leader = 31 - __clz(peers);
+        uint32_t before = 0;
+        if ((int)lane == leader) {
+            before = my_hist[d];
+            my_hist[d] = before + __popc(peers);
+        }
+        before = __shfl_sync(0xffffffffu, before, leader);
+        rank[i] = (uint16_t)(before + __popc(peers & lt));
+        __syncwarp();
+    }
+    __syncthreads();
+
+    // ---- combine warps: per digit, exclusive prefix over warps + tile count
+    uint32_t real = 0;  // number of real (non-padding) keys of digit threadIdx.x in this tile
+    if (threadIdx.x < RADIX) {
+        uint32_t padded = 0;
+#pragma unroll
+        for (int w = 0; w < SORT_WARPS; w++) {
+            const uint32_t c = s_whist[w * RADIX + threadIdx.x];
+            s_whist[w * RADIX + threadIdx.x] = padded;
+            padded += c;
+        }
+        // the padding keys of a partial tile all carry the all-ones digit
+        real = padded - ((threadIdx.x == mask) ? (uint32_t)TILE - valid : 0u);
+        // publish as early as possible: later tiles are waiting on this
+        st_relaxed_u32(status + (size_t)tile * RADIX + threadIdx.x, (tile == 0 ? ST_INCLUSIVE : ST_PARTIAL) | real);
+        // exclusive scan of the 256 padded counts -> first tile rank of each digit
+        uint32_t inc = padded;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t up = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += up;
+        }
+        if (lane == 31) s_scan_warp[warp] = inc;
+        s_digit_start[threadIdx.x] = inc - padded;  // exclusive within this warp of digits
+    }
+    __syncthreads();
+    if (threadIdx.x < RADIX) {
+        uint32_t base = 0;
+        for (int w = 0; w < (int)warp; w++) base += s_scan_warp[w];
+        s_digit_start[threadIdx.x] += base;
+    }
+    __syncthreads();
+
+    // ---- scatter keys into shared memory in tile-rank order
+#pragma unroll
+    for (int i = 0; i < ITEMS; i++) {
+        const uint32_t d = (uint32_t)(key[i] >> shift) & mask;
+        const uint32_t r = s_digit_start[d] + my_hist[d] + rank[i];
+        rank[i] = (uint16_t)r;
+        s_keys[r] = key[i];
+    }
+
+    // ---- decoupled look-back, one thread per digit
+    if (threadIdx.x < RADIX) {
+        uint32_t excl = 0;
+        if (tile > 0) {
+            int64_t t = (int64_t)tile - 1;
+            while (true) {
+                uint32_t st;
+                do { st = ld_relaxed_u32(status + (size_t)t * RADIX + threadIdx.x); } while ((st >> 30) == 0);
+                excl += st & ST_VALUE;
+                if ((st >> 30) == 2) break;
+                t--;
+            }
+            st_relaxed_u32(status + (size_t)tile * RADIX + threadIdx.x, ST_INCLUSIVE | (excl + real));
+        }
+        s_global_off[threadIdx.x] = digit_base[threadIdx.x] + excl - s_digit_start[threadIdx.x];
+    }
+    __syncthreads();
+
+    // ---- write out: consecutive threads -> consecutive tile ranks -> runs of consecutive addresses
+#pragma unroll
+    for (int j = 0; j < ITEMS; j++) {
+        const uint32_t pos = j * SORT_THREADS + threadIdx.x;
+        if (pos < valid) {
+            const K k = s_keys[pos];
+            const uint32_t d = (uint32_t)(k >> shift) & mask;
+            keys_out[s_global_off[d] + pos] = k;
+        }
+    }
+    if (HAS_VALUES) {
+#pragma unroll
+        for (int i = 0; i < ITEMS; i++) s_vals[rank[i]] = val[i];
+        __syncthreads();
+#pragma unroll
+        for (int j = 0; j < ITEMS; j++) {
+            const uint32_t pos = j * SORT_THREADS + threadIdx.x;
+            if (pos < valid) {
+                const uint32_t d = (uint32_t)(s_keys[pos] >> shift) & mask;
+                vals_out[s_global_off[d] + pos] = s_vals[pos];
+            }
+        }
+    }
+}
+
+template <typename K, bool HAS_VALUES> constexpr size_t onesweep_smem() {
+    return sizeof(K) * SORT_THREADS * Tile<K>::ITEMS + sizeof(uint32_t) * SORT_WARPS * RADIX +
+           (HAS_VALUES ? sizeof(uint32_t) * SORT_THREADS * Tile<K>::ITEMS : 0);
+}
+
+// ------------------------------------------------------------ scratch layout
+struct SortLayout {
+    size_t ghist, tickets, status, status_bytes, tmp_keys, tmp_vals, idx_a, idx_b, total;
+    uint64_t tiles;
+};
+
+inline size_t align_up(size_t x) { return (x + 255) & ~(size_t)255; }
+
+SortLayout sort_layout(uint64_t n, uint32_t key_bytes, uint32_t value_bytes) {
+    SortLayout L;
+    const uint64_t tile = (uint64_t)SORT_THREADS * (key_bytes == 8 ? Tile<uint64_t>::ITEMS : Tile<uint32_t>::ITEMS);
+    L.tiles = (n + tile - 1) / tile;
+    if (L.tiles == 0) L.tiles = 1;
+    size_t off = 0;
+    L.ghist = off; off += align_up(sizeof(uint32_t) * MAX_PASSES * RADIX);
+    L.tickets = off; off += align_up(sizeof(uint32_t) * MAX_PASSES);
+    L.status = off;
+    L.status_bytes = align_up(sizeof(uint32_t) * RADIX * L.tiles);
+    off += L.status_bytes * key_bytes;  // one status array per 8-bit pass
+    L.tmp_keys = off; off += align_up((size_t)n * key_bytes);
+    const bool direct = value_bytes == 4, indirect = value_bytes != 0 && value_bytes != 4;
+    L.tmp_vals = off; if (direct || indirect) off += align_up((size_t)n * 4);
+    L.idx_a = off; if (indirect) off += align_up((size_t)n * 4);
+    L.idx_b = off; if (indirect) off += align_up((size_t)n * 4);
+    L.total = off;
+    return L;
+}
+
+__global__ void __launch_bounds__(256) iota_kernel(uint32_t* p, uint32_t n) {
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) p[i] = i;
+}
+
+template <typename K>
+int run_passes(const K* keys_in, K* keys_out, const uint32_t* vals_in, uint32_t* vals_out, uint32_t n,
+               uint32_t shift0, uint32_t bits, uint32_t npass, char* scratch, const SortLayout& L, cudaStream_t s) {
+    uint32_t* ghist = reinterpret_cast<uint32_t*>(scratch + L.ghist);
+    unsigned* tickets = reinterpret_cast<unsigned*>(scratch + L.tickets);
+    K* tmp_keys = reinterpret_cast<K*>(scratch + L.tmp_keys);
+    uint32_t* tmp_vals = reinterpret_cast<uint32_t*>(scratch + L.tmp_vals);
+    const bool has_vals = vals_in != nullptr;
+
+    // zero histograms, tickets and all status words in one go (contiguous)
+    COL_CUDA(cudaMemsetAsync(scratch, 0, L.status + L.status_bytes * npass, s));
+    {
+        uint64_t want = ((uint64_t)n + HIST_THREADS * HIST_ITEMS - 1) / (HIST_THREADS * HIST_ITEMS);
+        unsigned blocks = (unsigned)(want > COL_NUM_SMS * 4 ? COL_NUM_SMS * 4 : want);
+        histogram_kernel<K><<<blocks, HIST_THREADS, 0, s>>>(keys_in, n, ghist, shift0, bits, npass);
+        COL_CHECK_LAUNCH();
+        digit_base_kernel<<<npass, RADIX, 0, s>>>(ghist);
+        COL_CHECK_LAUNCH();
+    }
+    const uint32_t mask = (1u << bits) - 1;
+    for (uint32_t p = 0; p < npass; p++) {
+        // the last pass lands in *_out; earlier ones alternate tmp/out backwards from there
+        const bool to_out = ((npass - 1 - p) & 1u) == 0;
+        const K* kin = p == 0 ? keys_in : (to_out ? tmp_keys : keys_out);
+        K* kout = to_out ? keys_out : tmp_keys;
+        const uint32_t* vin = p == 0 ? vals_in : (to_out ? tmp_vals : vals_out);
+        uint32_t* vout = to_out ? vals_out : tmp_vals;
+        uint32_t* status = reinterpret_cast<uint32_t*>(scratch + L.status + L.status_bytes * p);
+        if (has_vals) {
+            constexpr size_t smem = onesweep_smem<K, true>();
+            COL_CUDA(cudaFuncSetAttribute(onesweep_kernel<K, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            onesweep_kernel<K, true><<<(unsigned)L.tiles, SORT_THREADS, smem, s>>>(
+                kin, kout, vin, vout, n, ghist + p * RADIX, status, tickets + p, shift0 + p * bits, mask);
+        } else {
+            constexpr size_t smem = onesweep_smem<K, false>();
+            COL_CUDA(cudaFuncSetAttribute(onesweep_kernel<K, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            onesweep_kernel<K, false><<<(unsigned)L.tiles, SORT_THREADS, smem, s>>>(
+                kin, kout, nullptr, nullptr, n, ghist + p * RADIX, status, tickets + p, shift0 + p * bits, mask);
+        }
+        COL_CHECK_LAUNCH();
+    }
+    return 0;
+}
+
+int sort_impl(const void* keys_in, void* keys_out, const void* vals_in, void* vals_out, uint64_t n,
+              uint32_t key_bytes, uint32_t value_bytes, uint32_t shift0, uint32_t bits, uint32_t npass,
+              void* scratch_v, cudaStream_t s) {
+    if (n == 0) return 0;
+    if (n > (1ull << 30)) return COL_ERR_TOO_LARGE;
+    char* scratch = reinterpret_cast<char*>(scratch_v);
+    const SortLayout L = sort_layout(n, key_bytes, value_bytes);
+    const bool have_vals = value_bytes != 0 && vals_in && vals_out;
+    const bool indirect = have_vals && value_bytes != 4;
+    const uint32_t* vin = have_vals ? (const uint32_t*)vals_in : nullptr;
+    uint32_t* vout = have_vals ? (uint32_t*)vals_out : nullptr;
+    if (indirect) {  // wide payloads: sort (key, index), then gather the payload once
+        uint32_t* ia = reinterpret_cast<uint32_t*>(scratch + L.idx_a);
+        iota_kernel<<<col_blocks(n, 256) > COL_NUM_SMS * 16 ? COL_NUM_SMS * 16 : col_blocks(n, 256), 256, 0, s>>>(ia, (uint32_t)n);
+        COL_CHECK_LAUNCH();
+        vin = ia;
+        vout = reinterpret_cast<uint32_t*>(scratch + L.idx_b);
+    }
+    int rc;
+    if (key_bytes == 4)
+        rc = run_passes<uint32_t>((const uint32_t*)keys_in, (uint32_t*)keys_out, vin, vout, (uint32_t)n, shift0, bits,
+                                  npass, scratch, L, s);
+    else
+        rc = run_passes<uint64_t>((const uint64_t*)keys_in, (uint64_t*)keys_out, vin, vout, (uint32_t)n, shift0, bits,
+                                  npass, scratch, L, s);
+    if (rc) return rc;
+    if (indirect) return col_gather(vals_in, vout, vals_out, n, value_bytes, 4, s);
+    return 0;
+}
+
+}  // namespace
+
+COL_API size_t col_sort_scratch_bytes(uint64_t n, uint32_t key_bytes, uint32_t value_bytes) {
+    if (key_bytes != 4 && key_bytes != 8) return 0;
+    return sort_layout(n, key_bytes, value_bytes).total;
+}
+
+COL_API int col_sort_pairs(const void* keys_in, void* keys_out, const void* vals_in, void* vals_out, uint64_t n,
+                           uint32_t key_bytes, uint32_t value_bytes, uint32_t end_bit, void* scratch, void* stream) {
+    if ((key_bytes != 4 && key_bytes != 8) || !scratch || (n && (!keys_in || !keys_out))) return COL_ERR_BAD_ARG;
+    if (end_bit == 0 || end_bit > key_bytes * 8) end_bit = key_bytes * 8;
+    const uint32_t npass = (end_bit + RADIX_BITS - 1) / RADIX_BITS;
+    return sort_impl(keys_in, keys_out, vals_in, vals_out, n, key_bytes, value_bytes, 0, RADIX_BITS, npass, scratch,
+                     col_stream(stream));
+}
+
+COL_API int col_radix_pass(const void* keys_in, void* keys_out, const void* vals_in, void* vals_out, uint64_t n,
+                           uint32_t key_bytes, uint32_t value_bytes, uint32_t radix_bits, uint32_t pass, void* scratch,
+                           void* stream) {
+    if ((key_bytes != 4 && key_bytes != 8) || !scratch || (n && (!keys_in || !keys_out))) return COL_ERR_BAD_ARG;
+    if (radix_bits == 0 || radix_bits > RADIX_BITS || (pass + 1) * radix_bits > key_bytes * 8) return COL_ERR_BAD_ARG;
+    return sort_impl(keys_in, keys_out, vals_in, vals_out, n, key_bytes, value_bytes, pass * radix_bits, radix_bits, 1,
+                     scratch, col_stream(stream));
+}

@@ -1,0 +1,185 @@
+/*
+ * collision_b200.h -- C ABI of libcollision_b200.so
+ *
+ * B200 (sm_100a) implementation of the LBVH sphere-collision hot path of
+ * kwohlfahrt/collision.  The reference has no FFI of its own (its boundary is
+ * Python over PyOpenCL), so every entry point below cites the reference kernel
+ * / enqueue site it replaces (paths relative to the reference checkout).
+ *
+ * Conventions
+ *   - extern "C", plain pointers and sizes, no C++/torch types.
+ *   - Every pointer is a DEVICE pointer unless its name starts with h_.
+ *   - Every call only ENQUEUES work on `stream` (a cudaStream_t passed as
+ *     void*): it never allocates, never synchronises, never reads back.
+ *   - Scratch is caller-provided; its size comes from the pure host function
+ *     *_scratch_bytes.  Scratch needs no initialisation by the caller.
+ *   - Return value: 0 on success, a cudaError_t value on a CUDA failure,
+ *     COL_ERR_* (negative) on a bad argument.  Nothing throws.
+ *   - Re-entrant for distinct (stream, scratch) pairs; no global state.
+ *   - Floating-point work is compiled with -fmad=false -prec-div=true
+ *     -ftz=false: IEEE, no contraction, correctly rounded division.
+ */
+#ifndef COLLISION_B200_H
+#define COLLISION_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define COL_F32 0
+#define COL_F64 1
+
+#define COL_ERR_BAD_ARG (-1)
+#define COL_ERR_TOO_LARGE (-2)
+#define COL_ERR_UNSUPPORTED (-3)
+
+/* ABI version of this header; bumped on any signature change. */
+int col_abi_version(void);
+/* Compute capability the kernels were built for (100 -> sm_100a). */
+int col_built_arch(void);
+
+/* ---------------------------------------------------------------- layouts
+ * struct Node (collision/collision.cl:42-53; numpy dtype collision/collision.py:9):
+ *   16 bytes {u32 parent; u32 right_edge; u32 data[2]} -- leaf: data[0] = id,
+ *   internal: data = children[2].  Array of 2n-1: internals [0, n-1), leaves
+ *   [n-1, 2n-1), node 0 = root.  NO_NODE = 0xFFFFFFFF.
+ * struct Bound (collision/collision.cl:123-126): {T min[4]; T max[4]} (3-vector
+ *   in 4 lanes): 32 bytes for f32, 64 bytes for f64; lane 3 is never meaningful.
+ * Coordinates: n slots of 4 lanes (xyz + ignored pad), collision/misc.py:62-68.
+ */
+typedef struct {
+    uint32_t parent;
+    uint32_t right_edge;
+    uint32_t data[2];
+} col_node;
+
+/* ----------------------------------------------------------------- reduce
+ * Replaces Reducer.reduce = bounds1 + bounds2 (collision/reduce.py:62-76,
+ * collision/reduce.cl:5-58) with the accumulator list of Bounds
+ * (collision/bounds.py:5): out_minmax = {min[lanes], max[lanes]} over n slots of
+ * `lanes` scalars (1, 2, 4, 8 or 16; a 3-vector is a 4-lane slot).  One launch.
+ * col_sum is the Summer accumulator (collision/summer.py:4-8): out = {sum[lanes]}. */
+size_t col_reduce_scratch_bytes(void);
+int col_bounds(const void* values, uint64_t n, int dtype, uint32_t lanes, void* out_minmax,
+               void* scratch, void* stream);
+int col_sum(const void* values, uint64_t n, int dtype, uint32_t lanes, void* out_sum,
+            void* scratch, void* stream);
+
+/* ----------------------------------------------------------------- Morton
+ * Replaces range (collision/collision.cl:8-10), the 0xFFFFFFFF padding fill
+ * (collision/collision.py:138-142) and calculateCodes/morton/expandBits
+ * (collision/collision.cl:14-40) in one pass: codes[i] for i < n, codes[i] =
+ * 0xFFFFFFFF for n <= i < n_padded, ids[i] = i for i < n_padded.  ids may be
+ * NULL (codes only, the kernel-level calculateCodes contract).
+ * range2x4 = {min[4], max[4]} as written by col_bounds. */
+int col_morton(uint32_t* codes, uint32_t* ids, const void* coords4, const void* range2x4,
+               int dtype, uint32_t n, uint32_t n_padded, void* stream);
+
+/* ------------------------------------------------------------------- scan
+ * Replaces PrefixScanner.prefix_sum (collision/scan.py:75-112; local_scan /
+ * block_scan, collision/scan.cl:5-36): in-place exclusive prefix sum of u32,
+ * wrapping mod 2^32, single pass (decoupled look-back).  If total_out is not
+ * NULL it receives the u64 (non-wrapping) grand total. */
+size_t col_scan_scratch_bytes(uint64_t n);
+int col_exclusive_scan_u32(uint32_t* data, uint64_t n, uint64_t* total_out, void* scratch,
+                           void* stream);
+
+/* ------------------------------------------------------------------- sort
+ * Replaces RadixSorter.sort (collision/radix.py:118-170; block_sort / scatter,
+ * collision/radix.cl:48-139) and its per-pass scans: STABLE LSD radix sort
+ * (8-bit digits, one-sweep with decoupled look-back) of n keys of key_bytes
+ * (4 or 8) with an optional payload of value_bytes (0, 4, 8, 16 or 32) per key.
+ * keys_in / vals_in are NOT modified (the reference clobbers them).  Only key
+ * bits [0, end_bit) are sorted on (end_bit = 0 -> all key bits); the Collider
+ * passes 30 because Morton codes are 30-bit.  n <= 2^30. */
+size_t col_sort_scratch_bytes(uint64_t n, uint32_t key_bytes, uint32_t value_bytes);
+int col_sort_pairs(const void* keys_in, void* keys_out, const void* vals_in, void* vals_out,
+                   uint64_t n, uint32_t key_bytes, uint32_t value_bytes, uint32_t end_bit,
+                   void* scratch, void* stream);
+/* One LSD pass in isolation (what block_sort + prefix_sum + scatter compute per
+ * pass, collision/radix.py:140-157): stable partition by the digit
+ * (key >> (pass * radix_bits)) & (2^radix_bits - 1), radix_bits <= 8. */
+int col_radix_pass(const void* keys_in, void* keys_out, const void* vals_in, void* vals_out,
+                   uint64_t n, uint32_t key_bytes, uint32_t value_bytes, uint32_t radix_bits,
+                   uint32_t pass, void* scratch, void* stream);
+
+/* ------------------------------------------------------------------- tree
+ * Replaces fillInternal + generateBVH/delta (collision/collision.cl:55-121) in
+ * one launch: writes all 2n-1 col_node records (leaves: id, right_edge;
+ * internals: children, right_edge; every non-root parent).  The two fields the
+ * reference never writes are set deterministically: nodes[0].parent = NO_NODE,
+ * leaf data[1] = NO_NODE.  ids_sorted may be NULL (internals + parents only,
+ * the kernel-level generateBVH contract; leaf id/right_edge left untouched). */
+int col_build_tree(const uint32_t* codes_sorted, const uint32_t* ids_sorted, void* nodes,
+                   uint32_t n, void* stream);
+/* fillInternal alone (collision/collision.cl:55-63). */
+int col_fill_leaves(void* nodes, const uint32_t* ids_sorted, uint32_t n, void* stream);
+
+/* ------------------------------------------------------------------ refit
+ * Replaces the flag clear (collision/collision.py:147-150), leafBounds and
+ * internalBounds (collision/collision.cl:128-162) in one launch after a flag
+ * memset: leaf boxes = coords[id] -/+ radii[id]; every leaf walks to the root,
+ * the second arrival at a node (atomic flag) merges the two child boxes.
+ * flags: 2n-1 u32 of scratch (cleared inside).  coords4/radii may be NULL to
+ * skip the leaf-box step (kernel-level internalBounds contract). */
+int col_refit(void* bounds, uint32_t* flags, const void* nodes, const void* coords4,
+              const void* radii, int dtype, uint32_t n, void* stream);
+int col_leaf_bounds(void* bounds, const void* coords4, const void* radii, const void* nodes,
+                    int dtype, uint32_t n, void* stream);
+
+/* --------------------------------------------------------------- traverse
+ * Replaces traverse/checkOverlap/isLeaf (collision/collision.cl:164-226).
+ *
+ * col_traverse_count: one thread per query leaf q in [q_begin, q_end) (sorted
+ * position): counts[q - q_begin] = number of reported pairs of that query.
+ *
+ * col_traverse_write: the same walk, writing row (id[q], id[leaf]) at
+ * offsets[q - q_begin] + k for the k-th hit of q in DFS order (child a before
+ * b) when that index < capacity: the deterministic order of the sequential
+ * work-item loop.  offsets = exclusive scan of counts (+ a base of the caller's
+ * choice, e.g. the pairs of lower ranks).
+ *
+ * col_traverse_atomic: the reference's own single-pass contract: rows appended
+ * through one global counter in ARBITRARY order, *counter ends as the true
+ * total even beyond capacity (collision.cl:202-204).  pairs may be NULL when
+ * capacity == 0 (count only).  counter must be zeroed by the caller.  */
+int col_traverse_count(uint32_t* counts, const void* nodes, const void* bounds, int dtype,
+                       uint32_t n, uint32_t q_begin, uint32_t q_end, void* stream);
+int col_traverse_write(uint32_t* pairs, uint64_t capacity, const uint32_t* offsets,
+                       uint64_t base, const void* nodes, const void* bounds, int dtype,
+                       uint32_t n, uint32_t q_begin, uint32_t q_end, void* stream);
+int col_traverse_atomic(uint32_t* pairs, uint32_t* counter, uint32_t capacity, const void* nodes,
+                        const void* bounds, int dtype, uint32_t n, uint32_t q_begin,
+                        uint32_t q_end, void* stream);
+
+/* ----------------------------------------------------------- find_offsets
+ * Replaces OffsetFinder.find_offsets (collision/offset.py:40-49,
+ * collision/offset.cl:3-12): for sorted unsigned values[n_values],
+ * offsets[v] = first i with values[i] >= v, for v in [0, n_offsets); entries
+ * above the maximum = n_values.  value_bytes / offset_bytes: 4 or 8. */
+int col_find_offsets(const void* values, uint64_t n_values, uint32_t value_bytes, void* offsets,
+                     uint64_t n_offsets, uint32_t offset_bytes, void* stream);
+
+/* --------------------------------------------------------- gather/scatter
+ * Replaces Indexer.gather / .scatter (collision/index.py:37-55,
+ * collision/index.cl:1-13): out[i] = in[idx[i]] / out[idx[i]] = in[i];
+ * value_bytes any multiple of 4 up to 128 (or 1, 2), index_bytes 4 or 8. */
+int col_gather(const void* in, const void* idx, void* out, uint64_t n, uint32_t value_bytes,
+               uint32_t index_bytes, void* stream);
+int col_scatter(const void* in, const void* idx, void* out, uint64_t n, uint32_t value_bytes,
+                uint32_t index_bytes, void* stream);
+
+/* utility: u32 fill (cl.enqueue_fill_buffer sites, e.g. collision/offset.py:43) */
+int col_fill_u32(uint32_t* dst, uint32_t value, uint64_t n, void* stream);
+/* range (collision/collision.cl:8-10): ids[i] = i for i < n */
+int col_range(uint32_t* ids, uint64_t n, void* stream);
+/* device-to-device copy of `bytes` (cl.enqueue_copy sites) */
+int col_copy(void* dst, const void* src, uint64_t bytes, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* COLLISION_B200_H */

@@ -1,0 +1,244 @@
+"""GPU parity tests of the LBVH path: every stage and the whole pipeline against
+the CPU oracle and the reference's golden vectors.  Mirrors upstream's
+tests/test_collision.py (kernel level) and tests/test_collision_py.py (object level).
+All calls go through the C ABI (via collision_b200's ctypes binding)."""
+import numpy as np
+import pytest
+
+import golden_data as G
+from gpu_util import dev_empty, to_dev, to_host
+
+pytestmark = pytest.mark.gpu
+
+Node = G.Node
+
+
+@pytest.fixture(scope="module", params=["float32", "float64"])
+def kernels(request, cuda_env):
+    from collision_b200.collision import CollisionProgram
+    dev, cq = cuda_env
+    return CollisionProgram(dev, request.param).kernels, np.dtype(request.param)
+
+
+def scene_range(coords, dt):
+    rng = np.zeros((2, 4), dt)
+    rng[0, :3] = coords.min(axis=0)
+    rng[1, :3] = coords.max(axis=0)
+    return rng
+
+
+def test_fill_internal(cuda_env, kernels):
+    # tests/test_collision.py:50-75
+    dev, cq = cuda_env
+    k, _ = kernels
+    n = 8
+    ids = np.random.RandomState(4).permutation(n).astype('uint32')
+    nodes_buf = dev_empty((2 * n - 1) * 16, fill=0)
+    k['fillInternal'](cq, (32,), None, nodes_buf, to_dev(ids), n).synchronize()
+    nodes = to_host(nodes_buf, Node, (2 * n - 1,))
+    np.testing.assert_equal(nodes['data'][n - 1:, 0], ids)
+    np.testing.assert_equal(nodes['right_edge'][n - 1:], np.arange(n))
+
+
+@pytest.mark.parametrize("codes,expected", [(G.FIG3_CODES, G.fig3_expected), (G.ODD_CODES, G.odd_expected)])
+def test_generate_bvh(cuda_env, kernels, codes, expected):
+    # tests/test_collision.py:78-179
+    dev, cq = cuda_env
+    k, _ = kernels
+    n = len(codes)
+    nodes_buf = dev_empty((2 * n - 1) * 16, fill=0)
+    e = k['fillInternal'](cq, (32,), None, nodes_buf, to_dev(np.arange(n, dtype='uint32')), n)
+    k['generateBVH'](cq, (32,), None, to_dev(codes), nodes_buf, n, wait_for=[e]).synchronize()
+    nodes = to_host(nodes_buf, Node, (2 * n - 1,))
+    exp, leaf_parents = expected()
+    leaf = n - 1
+    np.testing.assert_equal(nodes[1:leaf], exp[1:])
+    np.testing.assert_equal(nodes[['data', 'right_edge']][0], exp[['data', 'right_edge']][0])
+    np.testing.assert_equal(nodes['parent'][leaf:], leaf_parents)
+    np.testing.assert_equal(nodes['right_edge'][leaf:], np.arange(n))
+    np.testing.assert_equal(nodes['data'][leaf:, 0], np.arange(n))
+
+
+def test_problem_codes(cuda_env, kernels, oracle):
+    # tests/test_collision.py:425-480
+    dev, cq = cuda_env
+    k, _ = kernels
+    n = len(G.PROBLEM_CODES)
+    ids = np.arange(n, dtype='uint32')
+    nodes_buf = dev_empty((2 * n - 1) * 16, fill=0xFF)
+    k['fillInternal'](cq, (32,), None, nodes_buf, to_dev(ids), n)
+    k['generateBVH'](cq, (32,), None, to_dev(G.PROBLEM_CODES), nodes_buf, n).synchronize()
+    nodes = to_host(nodes_buf, Node, (2 * n - 1,))
+    want = oracle.build_tree(G.PROBLEM_CODES, ids, fill=0xFFFFFFFF)
+    np.testing.assert_equal(nodes, want)
+    assert (nodes['parent'][1:] < n - 1).all()
+
+
+def test_compute_bounds(cuda_env, kernels):
+    # tests/test_collision.py:182-248
+    dev, cq = cuda_env
+    k, dt = kernels
+    c = G.slots(G.REFIT_COORDS, dt)
+    nodes = G.refit_nodes()
+    bounds_buf = dev_empty(len(nodes) * 8 * dt.itemsize, fill=0)
+    flags_buf = dev_empty(len(nodes) * 4, fill=0xFF)   # the refit entry point clears them itself
+    nodes_buf = to_dev(nodes)
+    e = k['leafBounds'](cq, (32,), None, bounds_buf, to_dev(c), to_dev(np.ones(4, dt)), nodes_buf, 4)
+    k['internalBounds'](cq, (32,), None, bounds_buf, flags_buf, nodes_buf, 4, wait_for=[e]).synchronize()
+    b = to_host(bounds_buf, dt, (len(nodes), 2, 4))
+    np.testing.assert_equal(b[:, :, :3], G.REFIT_EXPECTED.astype(dt))
+
+
+def test_codes(cuda_env, kernels):
+    # tests/test_collision.py:251-298
+    dev, cq = cuda_env
+    k, dt = kernels
+    c = G.slots(G.SIX_COORDS, dt)
+    codes_buf = dev_empty(6 * 4)
+    k['calculateCodes'](cq, (32,), None, codes_buf, to_dev(c), to_dev(scene_range(G.SIX_COORDS, dt)), 6).synchronize()
+    np.testing.assert_equal(to_host(codes_buf, 'uint32', (6,)), G.SIX_CODES)
+
+
+def test_traverse(cuda_env, kernels):
+    # tests/test_collision.py:302-422: the reference's own kernel sequence, host mergesort for the sort
+    dev, cq = cuda_env
+    k, dt = kernels
+    n = 6
+    c = G.slots(G.SIX_COORDS, dt)
+    coords_buf, radii_buf = to_dev(c), to_dev(np.ones(n, dt))
+    codes_buf = dev_empty(n * 4)
+    k['calculateCodes'](cq, (32,), None, codes_buf, coords_buf, to_dev(scene_range(G.SIX_COORDS, dt)), n).synchronize()
+    codes = to_host(codes_buf, 'uint32', (n,))
+    order = np.argsort(codes, kind='mergesort').astype('uint32')
+    codes_buf = to_dev(codes[order])
+    nodes_buf = dev_empty((2 * n - 1) * 16, fill=0)
+    bounds_buf = dev_empty((2 * n - 1) * 8 * dt.itemsize, fill=0)
+    flags_buf = dev_empty((2 * n - 1) * 4, fill=0)
+    collisions_buf = dev_empty(2 * 2 * 4, fill=0xFF)
+    n_buf = dev_empty(4, fill=0)
+    k['fillInternal'](cq, (32,), None, nodes_buf, to_dev(order), n)
+    k['generateBVH'](cq, (32,), None, codes_buf, nodes_buf, n)
+    k['leafBounds'](cq, (32,), None, bounds_buf, coords_buf, radii_buf, nodes_buf, n)
+    k['internalBounds'](cq, (32,), None, bounds_buf, flags_buf, nodes_buf, n)
+    k['traverse'](cq, (32,), None, collisions_buf, n_buf, 2, nodes_buf, bounds_buf, n).synchronize()
+    assert to_host(n_buf, 'uint32', (1,))[0] == 2
+    assert G.canon(to_host(collisions_buf, 'uint32', (2, 2))) == G.SIX_PAIRS
+
+
+# ------------------------------------------------------------ object level
+def run_collider(cuda_env, collider, c, r, capacity, dt):
+    dev, cq = cuda_env
+    coords_buf, radii_buf = to_dev(c), to_dev(r.astype(dt))
+    n_buf = dev_empty(4, fill=0xFF)
+    col_buf = dev_empty(max(capacity, 1) * 8, fill=0xFF) if capacity else None
+    collider.get_collisions(cq, coords_buf, radii_buf, n_buf, col_buf, capacity).synchronize()
+    total = int(to_host(n_buf, 'uint32', (1,))[0])
+    pairs = to_host(col_buf, 'uint32', (capacity, 2))[:min(total, capacity)] if capacity else np.zeros((0, 2), 'u4')
+    return total, pairs
+
+
+def test_padded_size(cuda_env):
+    # tests/test_collision_py.py:40-46
+    from collision_b200.collision import Collider
+    dev, cq = cuda_env
+    for size, ngroups, group_size, expected in [(48, 3, 8, 48), (47, 3, 8, 48), (49, 3, 8, 64)]:
+        assert Collider(dev, size, ngroups, group_size).padded_size == expected
+
+
+@pytest.mark.parametrize("dt", ["float32", "float64"])
+@pytest.mark.parametrize("ordered", [True, False])
+def test_collision(cuda_env, dt, ordered):
+    # tests/test_collision_py.py:49-97
+    from collision_b200.collision import Collider
+    dev, cq = cuda_env
+    collider = Collider(dev, 6, 3, 8, np.dtype(dt), ordered=ordered)
+    total, pairs = run_collider(cuda_env, collider, G.slots(G.SIX_COORDS, dt), np.ones(6), 2, np.dtype(dt))
+    assert total == 2 and G.canon(pairs) == G.SIX_PAIRS
+
+
+@pytest.mark.parametrize("size,ngroups,group_size", [(120, 5, 8), (256, 4, 32), (317, 4, 16), (341, 4, 64),
+                                                     (2, 1, 8), (3, 1, 8), (5000, 8, 64)])
+@pytest.mark.parametrize("dt", ["float32", "float64"])
+def test_random_collision(cuda_env, oracle, size, ngroups, group_size, dt):
+    # tests/test_collision_py.py:100-150 -- plus stage-by-stage bit parity with the oracle
+    from collision_b200.collision import Collider
+    dev, cq = cuda_env
+    dt = np.dtype(dt)
+    c, r = G.random_spheres(size, dtype=dt, pad=np.nan)
+    want = oracle.collide(c, r)
+    collider = Collider(dev, size, ngroups, group_size, dt)
+    cap = want['total'] + 3
+    total, pairs = run_collider(cuda_env, collider, c, r, cap, dt)
+    n = size
+    np.testing.assert_equal(to_host(collider._codes_bufs[1], 'uint32', (n,)), want['sorted_codes'])
+    np.testing.assert_equal(to_host(collider._ids_bufs[1], 'uint32', (n,)), want['sorted_ids'])
+    nodes = to_host(collider._nodes_buf, Node, (2 * n - 1,))
+    np.testing.assert_equal(nodes[1:]['parent'], want['nodes'][1:]['parent'])
+    np.testing.assert_equal(nodes['right_edge'], want['nodes']['right_edge'])
+    np.testing.assert_equal(nodes['data'][:n - 1], want['nodes']['data'][:n - 1])
+    np.testing.assert_equal(nodes['data'][n - 1:, 0], want['nodes']['data'][n - 1:, 0])
+    b = to_host(collider._bounds_buf, dt, (2 * n - 1, 2, 4))
+    np.testing.assert_equal(b[:, :, :3], want['bounds'][:, :, :3])
+    assert total == want['total']
+    np.testing.assert_equal(pairs, want['pairs'])          # identical ORDER (deterministic compaction)
+    assert G.canon(pairs) == G.canon(oracle.brute_force(c, r))
+    # reference-style single pass: same set, arbitrary order
+    total2, pairs2 = run_collider(cuda_env, Collider(dev, size, ngroups, group_size, dt, ordered=False), c, r, cap, dt)
+    assert total2 == total
+    np.testing.assert_equal(G.lexsorted(pairs2), G.lexsorted(want['pairs']))
+
+
+@pytest.mark.parametrize("old,new", [((350, 8, 64), (351, 8, 64)), ((350, 8, 64), (351, None, None)),
+                                     ((351, 8, 64), (100, 4, 16))])
+def test_random_collision_resized(cuda_env, oracle, old, new):
+    # tests/test_collision_py.py:153-207
+    from collision_b200.collision import Collider
+    dev, cq = cuda_env
+    collider = Collider(dev, *old)
+    collider.resize(*new)
+    size = new[0]
+    c, r = G.random_spheres(size, pad=np.nan)
+    want = oracle.collide(c, r)
+    total, pairs = run_collider(cuda_env, collider, c, r, want['total'], np.dtype('float32'))
+    assert total == want['total']
+    np.testing.assert_equal(pairs, want['pairs'])
+
+
+@pytest.mark.parametrize("ordered", [True, False])
+def test_count_only_and_overflow(cuda_env, oracle, ordered):
+    # tests/test_collision_py.py:261-327
+    from collision_b200.collision import Collider
+    dev, cq = cuda_env
+    size = 1000
+    c, r = G.random_spheres(size)
+    want = oracle.collide(c, r)
+    collider = Collider(dev, size, 10, 32, ordered=ordered)
+    total, _ = run_collider(cuda_env, collider, c, r, 0, np.dtype('float32'))
+    assert total == want['total']
+    with pytest.raises(ValueError):
+        collider.get_collisions(cq, to_dev(c), to_dev(r), dev_empty(4), None, 5)
+    # capacity smaller than the total: counter still the true total, buffer not overrun
+    cap = 7
+    col_buf = dev_empty((cap + 4) * 8, fill=0xFF)
+    n_buf = dev_empty(4)
+    collider.get_collisions(cq, to_dev(c), to_dev(r), n_buf, col_buf, cap).synchronize()
+    assert int(to_host(n_buf, 'uint32', (1,))[0]) == want['total']
+    got = to_host(col_buf, 'uint32', (cap + 4, 2))
+    assert (got[cap:] == 0xFFFFFFFF).all()
+    if ordered:
+        np.testing.assert_equal(got[:cap], want['pairs'][:cap])
+    else:
+        assert G.canon(got[:cap]) <= G.canon(want['pairs'])
+
+
+def test_program_mismatch(cuda_env):
+    # tests/test_collision_py.py:329-336 style: shared programs must match
+    from collision_b200.collision import Collider, CollisionProgram
+    dev, cq = cuda_env
+    prog = CollisionProgram(dev, 'float64')
+    with pytest.raises(ValueError):
+        Collider(dev, 64, 4, 8, np.dtype('float32'), program=prog)
+    c = Collider(dev, 64, 4, 8, np.dtype('float64'), program=prog)
+    assert c.program is prog
+    with pytest.raises(ValueError):
+        CollisionProgram(dev, 'int32')
