@@ -1,0 +1,350 @@
+#!/usr/bin/env python
+"""bench.py -- the driver's benchmark contract for the LBVH sphere-collision path.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+A "step" is one full Collider.get_collisions() over one synthetic scene:
+scene bounds -> Morton codes -> stable radix sort -> Karras tree -> AABB refit ->
+traversal -> deterministic pair compaction, writing the whole pair list.
+
+Workload (BASELINE.json configs[1]): 2^20 spheres uniform in the unit cube,
+r = 0.5 * N^(-1/3) (about 8 box-overlap neighbours each, ~4.1 M reported pairs),
+float32 coordinates in 16-byte slots, seed 4.
+
+`value`  : spheres/s with the inputs already resident in HBM (device timed with
+           CUDA events per step, L2 flushed between steps, max over ranks).
+`e2e`    : the same metric through the public API with HOST (pinned) buffers:
+           every step copies coords+radii host->device and the pair count and
+           pair list device->host inside the timed region.
+`roofline`: the dominant kernel of the step, timed live with CUDA events on the
+           launching stream, against the measured HBM copy peak.
+`cpu_baseline` / `--impl reference`: the CPU oracle (a C/OpenMP restatement of the
+           reference's OpenCL kernels; the reference itself needs PyOpenCL + an
+           OpenCL ICD, neither of which exists on these boxes) on all host cores.
+
+N > 1 (torchrun, one rank per GPU): the scene is built once on rank 0, the tree
+(nodes + boxes) is NCCL-broadcast, every rank traverses its contiguous
+Morton-sorted query range, per-rank pair totals are all-gathered.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+from pathlib import Path
+
+import numpy as np
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+
+METRIC = "spheres_per_sec_full_lbvh_pipeline"
+UNIT = "spheres/s"
+N_SPHERES = 1 << 20
+SEED = 4
+
+
+def make_scene(n, seed=SEED):
+    """configs[1]: uniform spheres, ~8 neighbours each (host arrays, float32 slots)."""
+    rs = np.random.RandomState(seed)
+    coords = np.zeros((n, 4), np.float32)
+    coords[:, :3] = rs.random_sample((n, 3)).astype(np.float32)
+    radii = np.full(n, 0.5 * n ** (-1.0 / 3.0), np.float32)
+    return coords, radii
+
+
+def workload_config(n, extra=None):
+    cfg = {"workload": "configs[1]: {} uniform spheres in the unit cube, r=0.5*N^(-1/3) (~8 neighbours), "
+                       "full pipeline incl. ordered pair list".format(n),
+           "n_spheres": n, "coord_dtype": "float32", "seed": SEED,
+           "l2": "flushed between steps (256 MiB write)"}
+    cfg.update(extra or {})
+    return cfg
+
+
+def measured_hbm_peak():
+    p = ROOT / "MEASURED_PEAKS.json"
+    if p.exists():
+        return float(json.loads(p.read_text())["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+# ------------------------------------------------------------------ clocks
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index=0):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
+                 "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._pump, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.lines.append(line)
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in self.lines:
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0]))
+                mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for name, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ------------------------------------------------------- CPU oracle timing
+def time_cpu_oracle(n, steps, warmup, capacity_pairs=True):
+    """The oracle's full pipeline (oracle/collision_oracle.c, orc_pipeline_f32) on all
+    host cores over the SAME scene; returns (spheres/s, seconds per step, total pairs, cores)."""
+    import oracle
+    oracle.build()
+    coords, radii = make_scene(n)
+    pipe = oracle.Pipeline(n)
+    total, _ = pipe.run(coords, radii, 0)
+    cap = total if capacity_pairs else 0
+    for _ in range(warmup):
+        pipe.run(coords, radii, cap)
+    ts = []
+    for _ in range(steps):
+        t0 = time.perf_counter()
+        pipe.run(coords, radii, cap)
+        ts.append(time.perf_counter() - t0)
+    sec = float(np.mean(ts))
+    return n / sec, sec, total, oracle.num_threads()
+
+
+def run_reference(args):
+    """--impl reference: the reference's algorithm on the host cores.  The reference
+    package itself cannot run here (PyOpenCL and an OpenCL ICD are absent and not
+    installable), so this times the oracle port of it; see DESIGN.md."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    n = N_SPHERES
+    value, sec, total, cores = time_cpu_oracle(n, args.steps, args.warmup)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config(n, {"l2": "n/a (CPU)"}),
+        "pairs": total, "pairs_per_sec": total / sec,
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port",
+                         "sample": "every step = the whole {}-sphere scene, full pipeline incl. pair list".format(n)},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ---------------------------------------------------------------- our arm
+STAGE_BYTES = {   # algorithmic bytes per launch (SURVEY.md 8(d) / DESIGN.md), n spheres, m pairs
+    "bounds": lambda n, m: 16 * n,
+    "morton": lambda n, m: 24 * n,
+    "sort": lambda n, m: 68 * n,
+    "tree": lambda n, m: 40 * n,
+    "refit": lambda n, m: 192 * n,
+    "traverse_count": lambda n, m: 36 * n,
+    "scan": lambda n, m: 8 * n,
+    "traverse_write": lambda n, m: 36 * n + 8 * m,
+    "traverse_fused": lambda n, m: 36 * n + 8 * m,
+}
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from collision_b200 import _lib
+    from collision_b200.collision import Collider
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: collision_b200 has no CPU fallback")
+    dev = torch.device("cuda", local_rank)
+    torch.cuda.set_device(dev)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    _lib.lib()   # fail loudly if the sm_100a library is missing
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    n = N_SPHERES * world            # weak scaling: 2^20 query spheres per GPU
+    coords_h, radii_h = make_scene(n)
+    coords_pin = torch.from_numpy(coords_h).pin_memory()
+    radii_pin = torch.from_numpy(radii_h).pin_memory()
+    coords_d, radii_d = coords_pin.to(dev), radii_pin.to(dev)
+    cq = torch.cuda.Stream(dev)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+
+    if world == 1:
+        collider = Collider(dev, n, 8, 128)
+    else:
+        from collision_b200.sharded import ShardedCollider
+        collider = ShardedCollider(dev, n, 8, 128)
+    n_buf = torch.zeros(1, dtype=torch.int32, device=dev)
+
+    # size the pair buffer from a count-only call (the reference's own protocol)
+    collider.get_collisions(cq, coords_d, radii_d, n_buf, None, 0).synchronize()
+    total = int(n_buf.item()) & 0xFFFFFFFF
+    local_cap = collider.local_pairs if world > 1 else total
+    pairs_d = torch.empty(max(local_cap, 1) * 2, dtype=torch.int32, device=dev)
+    pairs_pin = torch.empty(max(local_cap, 1) * 2, dtype=torch.int32).pin_memory()
+    n_pin = torch.zeros(1, dtype=torch.int32).pin_memory()
+
+    def step():
+        return collider.get_collisions(cq, coords_d, radii_d, n_buf, pairs_d, local_cap)
+
+    for _ in range(max(args.warmup, 3)):
+        flush.fill_(0)
+        step()
+    barrier()
+
+    # ---- device-resident timing: K steps, one event pair per step, L2 flushed in between
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    collider.stage_events = []
+    launches0 = collider.kernel_launches
+    step_events = []
+    barrier()
+    for _ in range(args.steps):
+        flush.fill_(0)
+        cq.wait_stream(torch.cuda.current_stream())
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(cq)
+        step()
+        b.record(cq)
+        step_events.append((a, b))
+        torch.cuda.current_stream().wait_stream(cq)
+    barrier()
+    clocks = sampler.stop() if rank == 0 else None
+    step_ms = [a.elapsed_time(b) for a, b in step_events]
+    total_ms = float(sum(step_ms))
+    launches = collider.kernel_launches - launches0
+    marks = collider.stage_events
+    collider.stage_events = None
+    stage_ms = {}
+    for (n0, e0), (n1, e1) in zip(marks, marks[1:]):
+        if n1 != "begin":
+            stage_ms.setdefault(n1, []).append(e0.elapsed_time(e1))
+    stage_ms = {k: float(np.mean(v)) for k, v in stage_ms.items()}
+
+    # ---- end to end through the public API with host buffers
+    e2e_s = []
+    for i in range(max(args.warmup, 3) + args.steps):
+        flush.fill_(0)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        with torch.cuda.stream(cq):
+            coords_d.copy_(coords_pin, non_blocking=True)
+            radii_d.copy_(radii_pin, non_blocking=True)
+            collider.get_collisions(cq, coords_d, radii_d, n_buf, pairs_d, local_cap)
+            n_pin.copy_(n_buf, non_blocking=True)
+        cq.synchronize()
+        got = collider.local_pairs if world > 1 else (int(n_pin.item()) & 0xFFFFFFFF)
+        with torch.cuda.stream(cq):
+            pairs_pin[:got * 2].copy_(pairs_d[:got * 2], non_blocking=True)
+        cq.synchronize()
+        if i >= max(args.warmup, 3):
+            e2e_s.append(time.perf_counter() - t0)
+    e2e_sec = float(np.mean(e2e_s))
+
+    # ---- max over ranks
+    if world > 1:
+        t = torch.tensor([total_ms, e2e_sec], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        total_ms, e2e_sec = float(t[0]), float(t[1])
+    ms_per_step = total_ms / args.steps
+
+    if rank == 0:
+        peak, peak_src = measured_hbm_peak()
+        dom = max(stage_ms, key=stage_ms.get) if stage_ms else None
+        roofline = None
+        if dom:
+            q = n // world if dom.startswith("traverse") else n
+            m = local_cap if dom.startswith("traverse") else total
+            nbytes = STAGE_BYTES.get(dom, lambda a, b: 0)(q, m)
+            achieved = nbytes / stage_ms[dom] / 1e6
+            roofline = {"kernel": dom, "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                        "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                        "algorithmic_bytes": nbytes, "ms": stage_ms[dom],
+                        "share_of_step": stage_ms[dom] / ms_per_step}
+        stages = {k: {"ms": v, "GBps": STAGE_BYTES.get(k, lambda a, b: 0)(n, total) / v / 1e6 if v > 0 else None}
+                  for k, v in stage_ms.items()}
+        cpu = None
+        if world == 1 and not args.no_cpu:
+            v, sec, ctotal, cores = time_cpu_oracle(N_SPHERES, 12, 2)
+            assert ctotal == total, ("GPU and oracle disagree on the pair count", total, ctotal)
+            cpu = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
+                   "sample": "12 full runs of the same {}-sphere scene (full pipeline incl. pair list), "
+                             "oracle/collision_oracle.c with OpenMP".format(N_SPHERES)}
+        line = {
+            "metric": METRIC, "value": n / (ms_per_step * 1e-3), "unit": UNIT, "n_gpus": world,
+            "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic",
+            "config": workload_config(n, {"parallelism": "single GPU" if world == 1 else
+                                          "tree built on rank 0, NCCL broadcast, traversal sharded over {} "
+                                          "Morton ranges".format(world)}),
+            "pairs": total, "pairs_per_sec": total / (ms_per_step * 1e-3),
+            "e2e": {"value": n / e2e_sec, "unit": UNIT,
+                    "h2d_bytes_per_step": coords_pin.numel() * 4 + radii_pin.numel() * 4,
+                    "d2h_bytes_per_step": 4 + local_cap * 8, "ms_per_step": e2e_sec * 1e3},
+            "gpu_launches": launches,
+            "clocks": clocks, "roofline": roofline, "stages": stages, "cpu_baseline": cpu,
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -128,6 +128,11 @@ class Collider:
                 raise ValueError("Collider and program coord_dtype must match")
         self.program = program
         self._bufs_for = None   # device scratch is allocated on first use
+        # optional instrumentation: set `stage_events = []` to have every call
+        # append (stage name, torch.cuda.Event) marks on the launching stream;
+        # kernel_launches counts the kernels this object has enqueued
+        self.stage_events = None
+        self.kernel_launches = 0
 
     # -- scratch ----------------------------------------------------------
     def _ensure_scratch(self):
@@ -175,33 +180,51 @@ class Collider:
         n, code = self.size, self.program._code
         self._ensure_scratch()
         _lib.begin(cq, wait_for)
+        mark = self._mark
+        mark(cq, "begin", 0)
 
         _lib.check(L.col_bounds(P(coords_buf), n, code, 4, P(self._bounds_buf), P(self.reducer._ensure_scratch()), S),
                    "col_bounds")
+        mark(cq, "bounds", 1)
         _lib.check(L.col_morton(P(self._codes_bufs[0]), P(self._ids_bufs[0]), P(coords_buf), P(self._bounds_buf),
                                 code, n, self.padded_size, S), "col_morton")
+        mark(cq, "morton", 1)
         # padding keys are not needed by this sort: only the n real keys move
         _lib.check(L.col_sort_pairs(P(self._codes_bufs[0]), P(self._codes_bufs[1]), P(self._ids_bufs[0]),
                                     P(self._ids_bufs[1]), n, 4, 4, MORTON_BITS, P(self.sorter._ensure_scratch()), S),
                    "col_sort_pairs")
+        mark(cq, "sort", 2 + (MORTON_BITS + 7) // 8)   # histogram + digit bases + one launch per digit
         _lib.check(L.col_build_tree(P(self._codes_bufs[1]), P(self._ids_bufs[1]), P(self._nodes_buf), n, S),
                    "col_build_tree")
+        mark(cq, "tree", 1)
         _lib.check(L.col_refit(P(self._bounds_buf), P(self._flags_buf), P(self._nodes_buf), P(coords_buf),
                                P(radii_buf), code, n, S), "col_refit")
+        mark(cq, "refit", 1)
         if self.ordered:
             _lib.check(L.col_traverse_count(P(self._counts_buf), P(self._nodes_buf), P(self._bounds_buf), code,
                                             n, 0, n, S), "col_traverse_count")
+            mark(cq, "traverse_count", 1)
             _lib.check(L.col_exclusive_scan_u32(P(self._counts_buf), n, P(self._total_buf),
                                                 P(self._scan_scratch), S), "col_exclusive_scan_u32")
             # counter = true total (low 32 bits, as upstream's uint counter)
             _lib.check(L.col_copy(P(n_collisions_buf), P(self._total_buf), 4, S), "col_copy")
+            mark(cq, "scan", 1)
             if n_collisions > 0:
                 _lib.check(L.col_traverse_write(P(collisions_buf), n_collisions, P(self._counts_buf), 0,
                                                 P(self._nodes_buf), P(self._bounds_buf), code, n, 0, n, S),
                            "col_traverse_write")
+                mark(cq, "traverse_write", 1)
         else:
             _lib.check(L.col_fill_u32(P(n_collisions_buf), 0, 1, S), "col_fill_u32")
             _lib.check(L.col_traverse_atomic(P(collisions_buf), P(n_collisions_buf), n_collisions,
                                              P(self._nodes_buf), P(self._bounds_buf), code, n, 0, n, S),
                        "col_traverse_atomic")
+            mark(cq, "traverse_atomic", 1)
         return _lib.done(cq)
+
+    def _mark(self, cq, name, kernels):
+        self.kernel_launches += kernels
+        if self.stage_events is not None:
+            ev = torch.cuda.Event(enable_timing=True)
+            ev.record(cq)
+            self.stage_events.append((name, ev))
