@@ -107,11 +107,17 @@ class Collider:
     id_dtype = dtype('uint32')
 
     def __init__(self, ctx, size, ngroups, group_size, coord_dtype=dtype('float32'),
-                 program=None, sorter_programs=(None, None), reducer_program=None, ordered=True):
+                 program=None, sorter_programs=(None, None), reducer_program=None, ordered=True,
+                 layout="wide"):
         coord_dtype = dtype(coord_dtype)
         self.size = size
         self.group_size = group_size
         self.ordered = ordered
+        # "wide": traversal records + single-pass compaction (default, needs ordered=True);
+        # "reference": only the reference's Node / Bound arrays are used
+        if layout not in ("wide", "reference"):
+            raise ValueError("layout must be 'wide' or 'reference'")
+        self.fast = layout == "wide" and ordered
 
         self.sorter = RadixSorter(
             ctx, self.padded_size, group_size,
@@ -151,6 +157,8 @@ class Collider:
         self._counts_buf = _lib.alloc_bytes(ctx, self.size * 4)
         self._scan_scratch = _lib.alloc_bytes(ctx, L.col_scan_scratch_bytes(self.size))
         self._total_buf = torch.zeros(1, dtype=torch.int64, device=ctx)
+        self._wide_buf = _lib.alloc_bytes(ctx, max(self.size - 1, 1) * 16 * self.program.coord_dtype.itemsize)
+        self._trv_scratch = _lib.alloc_bytes(ctx, L.col_traverse_scratch_bytes(self.size))
         self._bufs_for = key
 
     def resize(self, size=None, ngroups=None, group_size=None, radix_bits=None):
@@ -187,13 +195,49 @@ class Collider:
                    "col_bounds")
         mark(cq, "bounds", 1)
         _lib.check(L.col_morton(P(self._codes_bufs[0]), P(self._ids_bufs[0]), P(coords_buf), P(self._bounds_buf),
-                                code, n, self.padded_size, S), "col_morton")
+                                code, n, n, S), "col_morton")
         mark(cq, "morton", 1)
         # padding keys are not needed by this sort: only the n real keys move
         _lib.check(L.col_sort_pairs(P(self._codes_bufs[0]), P(self._codes_bufs[1]), P(self._ids_bufs[0]),
                                     P(self._ids_bufs[1]), n, 4, 4, MORTON_BITS, P(self.sorter._ensure_scratch()), S),
                    "col_sort_pairs")
         mark(cq, "sort", 2 + (MORTON_BITS + 7) // 8)   # histogram + digit bases + one launch per digit
+        if self.fast:
+            self._traverse_fast(cq, coords_buf, radii_buf, n_collisions_buf, collisions_buf, n_collisions)
+        else:
+            self._traverse_reference_layout(cq, coords_buf, radii_buf, n_collisions_buf, collisions_buf, n_collisions)
+        return _lib.done(cq)
+
+    def _mark(self, cq, name, kernels):
+        self.kernel_launches += kernels
+        if self.stage_events is not None:
+            ev = torch.cuda.Event(enable_timing=True)
+            ev.record(cq)
+            self.stage_events.append((name, ev))
+
+    def _traverse_fast(self, cq, coords_buf, radii_buf, n_collisions_buf, collisions_buf, n_collisions):
+        """Tree + refit emitting the traversal records, then ONE launch that walks
+        every query once and commits its rows in the deterministic order."""
+        L, P, S = _lib.lib(), _lib.ptr, _lib.stream_ptr(cq)
+        n, code, mark = self.size, self.program._code, self._mark
+        _lib.check(L.col_build_tree_wide(P(self._codes_bufs[1]), P(self._ids_bufs[1]), P(self._nodes_buf),
+                                         P(self._wide_buf), code, n, S), "col_build_tree_wide")
+        mark(cq, "tree", 1)
+        _lib.check(L.col_refit_wide(P(self._bounds_buf), P(self._wide_buf), P(self._flags_buf), P(self._nodes_buf),
+                                    P(coords_buf), P(radii_buf), code, n, S), "col_refit_wide")
+        mark(cq, "refit", 1)
+        _lib.check(L.col_traverse_wide_fused(P(collisions_buf), n_collisions, 0, P(self._total_buf),
+                                             P(self._wide_buf), P(self._bounds_buf), P(self._ids_bufs[1]), code,
+                                             n, 0, n, P(self._trv_scratch), S), "col_traverse_wide_fused")
+        # counter = true total (low 32 bits, as upstream's uint counter)
+        _lib.check(L.col_copy(P(n_collisions_buf), P(self._total_buf), 4, S), "col_copy")
+        mark(cq, "traverse_fused" if n_collisions else "traverse_count", 1)
+
+    def _traverse_reference_layout(self, cq, coords_buf, radii_buf, n_collisions_buf, collisions_buf, n_collisions):
+        """The same stages on the reference's Node / Bound arrays only (kernel-level
+        contract of collision.cl); count -> scan -> write, or one atomic counter."""
+        L, P, S = _lib.lib(), _lib.ptr, _lib.stream_ptr(cq)
+        n, code, mark = self.size, self.program._code, self._mark
         _lib.check(L.col_build_tree(P(self._codes_bufs[1]), P(self._ids_bufs[1]), P(self._nodes_buf), n, S),
                    "col_build_tree")
         mark(cq, "tree", 1)
@@ -220,11 +264,3 @@ class Collider:
                                              P(self._nodes_buf), P(self._bounds_buf), code, n, 0, n, S),
                        "col_traverse_atomic")
             mark(cq, "traverse_atomic", 1)
-        return _lib.done(cq)
-
-    def _mark(self, cq, name, kernels):
-        self.kernel_launches += kernels
-        if self.stage_events is not None:
-            ev = torch.cuda.Event(enable_timing=True)
-            ev.record(cq)
-            self.stage_events.append((name, ev))

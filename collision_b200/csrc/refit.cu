@@ -108,6 +108,94 @@ refit_kernel(T* __restrict__ bounds, uint32_t* __restrict__ flags, const col_nod
     }
 }
 
+// ---- traversal ("wide") nodes -------------------------------------------
+// One record of 16 scalars per internal node, laid out for the traversal:
+//   [0..5]  box of child a (lo xyz, hi xyz)     [6..11] box of child b
+//   [12..15] (as u32 x4, in the first 16 bytes) child a, child b, right_edge a, right_edge b
+// 64 bytes for f32 / 128 for f64: everything a visit needs comes from one
+// contiguous record instead of five cache lines of the Node/Bound arrays.  The
+// index part is written by the tree kernel; here each arriving thread stores
+// its own child's box into its half BEFORE announcing its arrival, and the
+// second arrival reads the other half (so no Bound array is needed for the
+// walk itself).  The Node/Bound arrays are still filled (reference layout).
+template <typename T>
+__device__ __forceinline__ void store_half(T* wide, size_t node, int half, const Box<T>& b) {
+    T* p = wide + node * 16 + half * 6;
+    if constexpr (sizeof(T) == 4) {
+        if (half == 0) {
+            *reinterpret_cast<float4*>(p) = make_float4(b.lo[0], b.lo[1], b.lo[2], b.hi[0]);
+            *reinterpret_cast<float2*>(p + 4) = make_float2(b.hi[1], b.hi[2]);
+        } else {
+            *reinterpret_cast<float2*>(p) = make_float2(b.lo[0], b.lo[1]);
+            *reinterpret_cast<float4*>(p + 2) = make_float4(b.lo[2], b.hi[0], b.hi[1], b.hi[2]);
+        }
+    } else {
+        double2* q = reinterpret_cast<double2*>(p);
+        q[0] = make_double2(b.lo[0], b.lo[1]);
+        q[1] = make_double2(b.lo[2], b.hi[0]);
+        q[2] = make_double2(b.hi[1], b.hi[2]);
+    }
+}
+template <typename T>
+__device__ __forceinline__ Box<T> load_half_cg(const T* wide, size_t node, int half) {
+    const T* p = wide + node * 16 + half * 6;
+    Box<T> b;
+    if constexpr (sizeof(T) == 4) {
+        float v[6];
+        if (half == 0) {
+            const float4 a = ld_cg_f4(reinterpret_cast<const float4*>(p));
+            float2 c;
+            asm volatile("ld.global.cg.v2.f32 {%0,%1}, [%2];" : "=f"(c.x), "=f"(c.y) : "l"(p + 4) : "memory");
+            v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = c.x; v[5] = c.y;
+        } else {
+            float2 c;
+            asm volatile("ld.global.cg.v2.f32 {%0,%1}, [%2];" : "=f"(c.x), "=f"(c.y) : "l"(p) : "memory");
+            const float4 a = ld_cg_f4(reinterpret_cast<const float4*>(p + 2));
+            v[0] = c.x; v[1] = c.y; v[2] = a.x; v[3] = a.y; v[4] = a.z; v[5] = a.w;
+        }
+        b.lo[0] = v[0]; b.lo[1] = v[1]; b.lo[2] = v[2]; b.hi[0] = v[3]; b.hi[1] = v[4]; b.hi[2] = v[5];
+    } else {
+        const double2* q = reinterpret_cast<const double2*>(p);
+        const double2 a = ld_cg_d2(q), c = ld_cg_d2(q + 1), d = ld_cg_d2(q + 2);
+        b.lo[0] = a.x; b.lo[1] = a.y; b.lo[2] = c.x; b.hi[0] = c.y; b.hi[1] = d.x; b.hi[2] = d.y;
+    }
+    return b;
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+refit_wide_kernel(T* __restrict__ bounds, T* __restrict__ wide, uint32_t* __restrict__ flags,
+                  const col_node* __restrict__ nodes, const T* __restrict__ coords, const T* __restrict__ radii,
+                  uint32_t n) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t leaf_start = n - 1;
+    uint32_t node = leaf_start + i;
+    const uint4 leaf = __ldg(reinterpret_cast<const uint4*>(nodes + node));  // {parent, right_edge, id, -}
+    Box<T> box = leaf_box<T>(coords, radii, leaf.z);
+    store_box(bounds, node, box);
+    if (n < 2) return;
+    uint32_t parent = leaf.x;
+    while (true) {
+        const uint4 rec = __ldg(reinterpret_cast<const uint4*>(nodes + parent));  // {grandparent, right_edge, a, b}
+        const int half = rec.z == node ? 0 : 1;
+        store_half(wide, parent, half, box);
+        __threadfence();  // my half is visible before my arrival is
+        if (atomicAdd(flags + parent, 1u) < 1u) return;  // first to arrive: the sibling carries on
+        __threadfence();
+        const Box<T> other = load_half_cg(wide, parent, half ^ 1);
+#pragma unroll
+        for (int k = 0; k < 3; k++) {
+            box.lo[k] = vmin(box.lo[k], other.lo[k]);
+            box.hi[k] = vmax(box.hi[k], other.hi[k]);
+        }
+        store_box(bounds, parent, box);
+        node = parent;
+        if (node == 0) return;
+        parent = rec.x;
+    }
+}
+
 template <typename T>
 __global__ void __launch_bounds__(256)
 leaf_bounds_kernel(T* __restrict__ bounds, const T* __restrict__ coords, const T* __restrict__ radii,
@@ -138,6 +226,23 @@ COL_API int col_refit(void* bounds, uint32_t* flags, const void* nodes, const vo
     } else {
         return COL_ERR_UNSUPPORTED;
     }
+    COL_CHECK_LAUNCH();
+    return 0;
+}
+
+COL_API int col_refit_wide(void* bounds, void* wide, uint32_t* flags, const void* nodes, const void* coords4,
+                           const void* radii, int dtype, uint32_t n, void* stream) {
+    if (!bounds || !wide || !flags || !nodes || !coords4 || !radii) return COL_ERR_BAD_ARG;
+    if (n == 0) return 0;
+    cudaStream_t s = col_stream(stream);
+    COL_CUDA(cudaMemsetAsync(flags, 0, sizeof(uint32_t) * (n > 1 ? n - 1 : 1), s));  // only internal nodes count arrivals
+    const unsigned blocks = col_blocks(n, 256);
+    if (dtype == COL_F32)
+        refit_wide_kernel<float><<<blocks, 256, 0, s>>>((float*)bounds, (float*)wide, flags, (const col_node*)nodes, (const float*)coords4, (const float*)radii, n);
+    else if (dtype == COL_F64)
+        refit_wide_kernel<double><<<blocks, 256, 0, s>>>((double*)bounds, (double*)wide, flags, (const col_node*)nodes, (const double*)coords4, (const double*)radii, n);
+    else
+        return COL_ERR_UNSUPPORTED;
     COL_CHECK_LAUNCH();
     return 0;
 }

@@ -20,6 +20,8 @@
 // Traffic: 4n + passes * 2 * (key + value) * n bytes -> 68 B per (u32, u32)
 // pair, 36 B per u32 key: the HBM roofline of the op.  Stability is part of
 // the contract (the sorted position is the leaf index of the tree).
+#include <cstdlib>
+
 #include "common.cuh"
 
 namespace {
@@ -90,7 +92,7 @@ __global__ void __launch_bounds__(RADIX) digit_base_kernel(uint32_t* ghist) {
 }
 
 // ----------------------------------------------------------------- onesweep
-template <typename K, bool HAS_VALUES>
+template <typename K, bool HAS_VALUES, int RANK>
 __global__ void __launch_bounds__(SORT_THREADS, 2)
 onesweep_kernel(const K* __restrict__ keys_in, K* __restrict__ keys_out, const uint32_t* __restrict__ vals_in,
                 uint32_t* __restrict__ vals_out, uint32_t n, const uint32_t* __restrict__ digit_base,
@@ -124,6 +126,41 @@ onesweep_kernel(const K* __restrict__ keys_in, K* __restrict__ keys_out, const u
         const uint32_t e = warp_off + i * 32 + lane;
         key[i] = e < valid ? keys_in[tile_base + e] : (K)~(K)0;  // padding sorts last within the tile
     }
+
+    // ---- rank inside the warp (stable): peers = lanes of this row holding the
+    // same digit; the highest peer bumps the warp's digit counter once for all of
+    // them (an ordered shared-memory atomic, no warp barrier needed), every peer
+    // ranks itself by the number of lower peers.  All the match operations are
+    // issued before any of the dependent counter updates so their latencies overlap.
+    uint32_t* my_hist = s_whist + warp * RADIX;
+    uint16_t rank[ITEMS];
+    const unsigned lt = lanemask_lt();
+    unsigned peers[ITEMS];
+#pragma unroll
+    for (int i = 0; i < ITEMS; i++) {
+        const uint32_t d = (uint32_t)(key[i] >> shift) & mask;
+        if (RANK == 2) {  // ballot multi-split over the 8 digit bits
+            unsigned p = 0xffffffffu;
+#pragma unroll
+            for (int b = 0; b < RADIX_BITS; b++) {
+                const unsigned vote = __ballot_sync(0xffffffffu, (d >> b) & 1u);
+                p &= ((d >> b) & 1u) ? vote : ~vote;
+            }
+            peers[i] = p;
+        } else {
+            peers[i] = __match_any_sync(0xffffffffu, d);
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < ITEMS; i++) {
+        const uint32_t d = (uint32_t)(key[i] >> shift) & mask;
+        const int leader = 31 - __clz(peers[i]);
+        uint32_t before = 0;
+        if ((int)lane == leader) before = atomicAdd(&my_hist[d], (uint32_t)__popc(peers[i]));
+        before = __shfl_sync(0xffffffffu, before, leader);
+        rank[i] = (uint16_t)(before + __popc(peers[i] & lt));
+    }
+    // payload loads are issued here so that their latency hides behind the combine phase
     uint32_t val[HAS_VALUES ? ITEMS : 1];
     if (HAS_VALUES) {
 #pragma unroll
@@ -131,25 +168,6 @@ onesweep_kernel(const K* __restrict__ keys_in, K* __restrict__ keys_out, const u
             const uint32_t e = warp_off + i * 32 + lane;
             val[i] = e < valid ? vals_in[tile_base + e] : 0u;
         }
-    }
-
-    // ---- rank inside the warp (stable)
-    uint32_t* my_hist = s_whist + warp * RADIX;
-    uint16_t rank[ITEMS];
-    const unsigned lt = lanemask_lt();
-#pragma unroll
-    for (int i = 0; i < ITEMS; i++) {
-        const uint32_t d = (uint32_t)(key[i] >> shift) & mask;
-        const unsigned peers = __match_any_sync(0xffffffffu, d);
-        const int leader = 31 - __clz(peers);
-        uint32_t before = 0;
-        if ((int)lane == leader) {
-            before = my_hist[d];
-            my_hist[d] = before + __popc(peers);
-        }
-        before = __shfl_sync(0xffffffffu, before, leader);
-        rank[i] = (uint16_t)(before + __popc(peers & lt));
-        __syncwarp();
     }
     __syncthreads();
 
@@ -294,6 +312,7 @@ int run_passes(const K* keys_in, K* keys_out, const uint32_t* vals_in, uint32_t*
         COL_CHECK_LAUNCH();
     }
     const uint32_t mask = (1u << bits) - 1;
+    static const int rank_mode = getenv("COL_SORT_RANK") ? atoi(getenv("COL_SORT_RANK")) : 1;  // tuning aid
     for (uint32_t p = 0; p < npass; p++) {
         // the last pass lands in *_out; earlier ones alternate tmp/out backwards from there
         const bool to_out = ((npass - 1 - p) & 1u) == 0;
@@ -302,17 +321,21 @@ int run_passes(const K* keys_in, K* keys_out, const uint32_t* vals_in, uint32_t*
         const uint32_t* vin = p == 0 ? vals_in : (to_out ? tmp_vals : vals_out);
         uint32_t* vout = to_out ? vals_out : tmp_vals;
         uint32_t* status = reinterpret_cast<uint32_t*>(scratch + L.status + L.status_bytes * p);
+#define LAUNCH_ONESWEEP(HV, RK)                                                                              \
+    {                                                                                                        \
+        constexpr size_t smem = onesweep_smem<K, HV>();                                                      \
+        COL_CUDA(cudaFuncSetAttribute(onesweep_kernel<K, HV, RK>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
+                                      (int)smem));                                                           \
+        onesweep_kernel<K, HV, RK><<<(unsigned)L.tiles, SORT_THREADS, smem, s>>>(                            \
+            kin, kout, HV ? vin : nullptr, HV ? vout : nullptr, n, ghist + p * RADIX, status, tickets + p,   \
+            shift0 + p * bits, mask);                                                                        \
+    }
         if (has_vals) {
-            constexpr size_t smem = onesweep_smem<K, true>();
-            COL_CUDA(cudaFuncSetAttribute(onesweep_kernel<K, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-            onesweep_kernel<K, true><<<(unsigned)L.tiles, SORT_THREADS, smem, s>>>(
-                kin, kout, vin, vout, n, ghist + p * RADIX, status, tickets + p, shift0 + p * bits, mask);
+            if (rank_mode == 2) LAUNCH_ONESWEEP(true, 2) else LAUNCH_ONESWEEP(true, 1)
         } else {
-            constexpr size_t smem = onesweep_smem<K, false>();
-            COL_CUDA(cudaFuncSetAttribute(onesweep_kernel<K, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-            onesweep_kernel<K, false><<<(unsigned)L.tiles, SORT_THREADS, smem, s>>>(
-                kin, kout, nullptr, nullptr, n, ghist + p * RADIX, status, tickets + p, shift0 + p * bits, mask);
+            if (rank_mode == 2) LAUNCH_ONESWEEP(false, 2) else LAUNCH_ONESWEEP(false, 1)
         }
+#undef LAUNCH_ONESWEEP
         COL_CHECK_LAUNCH();
     }
     return 0;

@@ -155,6 +155,39 @@ int col_traverse_atomic(uint32_t* pairs, uint32_t* counter, uint32_t capacity, c
                         const void* bounds, int dtype, uint32_t n, uint32_t q_begin,
                         uint32_t q_end, void* stream);
 
+/* ------------------------------------------------- Collider fast path ("wide")
+ * The entry points above keep the reference's Node/Bound kernel contract.  The
+ * Collider itself (collision/collision.py:171-196: fillInternal, generateBVH,
+ * leafBounds, internalBounds, traverse) runs on a traversal-oriented copy of the
+ * tree that the build and refit kernels emit alongside the Node/Bound arrays:
+ * one record of 16 scalars per internal node (64 B f32 / 128 B f64):
+ *   [0..5] box of child a (lo xyz, hi xyz)   [6..11] box of child b
+ *   [12..15] as 4 x u32 in the first 16 bytes: child a, child b,
+ *            right_edge(child a), right_edge(child b)
+ * `wide`: (n-1) such records.  `bounds` (Bound array) still receives every box;
+ * the traversal reads only its leaf part (the query boxes).  The arithmetic and
+ * the reported rows are identical to the entry points above.
+ *
+ * col_traverse_wide_fused: one walk per query + deterministic compaction in ONE
+ * launch (decoupled look-back over blocks of 128 queries): row k of query q
+ * lands at base + (number of rows of queries q_begin..q-1) + k when that index
+ * is < capacity; *total_out (u64, may be NULL) = rows found in the range.
+ * capacity == 0: count only.  ids_sorted: ids in sorted order (the sort's
+ * payload output). */
+int col_build_tree_wide(const uint32_t* codes_sorted, const uint32_t* ids_sorted, void* nodes, void* wide,
+                        int dtype, uint32_t n, void* stream);
+int col_refit_wide(void* bounds, void* wide, uint32_t* flags, const void* nodes, const void* coords4,
+                   const void* radii, int dtype, uint32_t n, void* stream);
+size_t col_traverse_scratch_bytes(uint32_t n_queries);
+int col_traverse_wide_count(uint64_t* total, uint32_t* counts, const void* wide, const void* bounds, int dtype,
+                            uint32_t n, uint32_t q_begin, uint32_t q_end, void* stream);
+int col_traverse_wide_fused(uint32_t* pairs, uint64_t capacity, uint64_t base, uint64_t* total_out,
+                            const void* wide, const void* bounds, const uint32_t* ids_sorted, int dtype,
+                            uint32_t n, uint32_t q_begin, uint32_t q_end, void* scratch, void* stream);
+int col_traverse_wide_write(uint32_t* pairs, uint64_t capacity, const uint32_t* offsets, uint64_t base,
+                            const void* wide, const void* bounds, const uint32_t* ids_sorted, int dtype,
+                            uint32_t n, uint32_t q_begin, uint32_t q_end, void* stream);
+
 /* ----------------------------------------------------------- find_offsets
  * Replaces OffsetFinder.find_offsets (collision/offset.py:40-49,
  * collision/offset.cl:3-12): for sorted unsigned values[n_values],

@@ -159,14 +159,15 @@ def test_collision(cuda_env, dt, ordered):
 @pytest.mark.parametrize("size,ngroups,group_size", [(120, 5, 8), (256, 4, 32), (317, 4, 16), (341, 4, 64),
                                                      (2, 1, 8), (3, 1, 8), (5000, 8, 64)])
 @pytest.mark.parametrize("dt", ["float32", "float64"])
-def test_random_collision(cuda_env, oracle, size, ngroups, group_size, dt):
+@pytest.mark.parametrize("layout", ["wide", "reference"])
+def test_random_collision(cuda_env, oracle, size, ngroups, group_size, dt, layout):
     # tests/test_collision_py.py:100-150 -- plus stage-by-stage bit parity with the oracle
     from collision_b200.collision import Collider
     dev, cq = cuda_env
     dt = np.dtype(dt)
     c, r = G.random_spheres(size, dtype=dt, pad=np.nan)
     want = oracle.collide(c, r)
-    collider = Collider(dev, size, ngroups, group_size, dt)
+    collider = Collider(dev, size, ngroups, group_size, dt, layout=layout)
     cap = want['total'] + 3
     total, pairs = run_collider(cuda_env, collider, c, r, cap, dt)
     n = size
@@ -204,15 +205,15 @@ def test_random_collision_resized(cuda_env, oracle, old, new):
     np.testing.assert_equal(pairs, want['pairs'])
 
 
-@pytest.mark.parametrize("ordered", [True, False])
-def test_count_only_and_overflow(cuda_env, oracle, ordered):
+@pytest.mark.parametrize("ordered,layout", [(True, "wide"), (True, "reference"), (False, "reference")])
+def test_count_only_and_overflow(cuda_env, oracle, ordered, layout):
     # tests/test_collision_py.py:261-327
     from collision_b200.collision import Collider
     dev, cq = cuda_env
     size = 1000
     c, r = G.random_spheres(size)
     want = oracle.collide(c, r)
-    collider = Collider(dev, size, 10, 32, ordered=ordered)
+    collider = Collider(dev, size, 10, 32, ordered=ordered, layout=layout)
     total, _ = run_collider(cuda_env, collider, c, r, 0, np.dtype('float32'))
     assert total == want['total']
     with pytest.raises(ValueError):
@@ -242,3 +243,66 @@ def test_program_mismatch(cuda_env):
     assert c.program is prog
     with pytest.raises(ValueError):
         CollisionProgram(dev, 'int32')
+
+
+@pytest.mark.parametrize("dt", ["float32", "float64"])
+def test_dense_cluster_overflows_stash(cuda_env, oracle, dt):
+    """Many more than 32 hits per query (the fused kernel's stash) and heavy code
+    duplication: exercises the second walk and the duplicate tie-break."""
+    from collision_b200.collision import Collider
+    dev, cq = cuda_env
+    dt = np.dtype(dt)
+    rs = np.random.RandomState(7)
+    n = 3000
+    c = np.zeros((n, 4), dt)
+    c[:, :3] = rs.normal(0.5, 0.01, (n, 3))
+    c[::3] = c[1::3][:len(c[::3])]                      # exact duplicates
+    r = np.full(n, 0.004, dt)
+    want = oracle.collide(c, r)
+    assert want['counts'].max() > 64
+    total, pairs = run_collider(cuda_env, Collider(dev, n, 8, 64, dt), c, r, want['total'], dt)
+    assert total == want['total']
+    np.testing.assert_equal(pairs, want['pairs'])
+    # a range-limited capacity still yields the first rows
+    total, pairs = run_collider(cuda_env, Collider(dev, n, 8, 64, dt), c, r, 1000, dt)
+    assert total == want['total']
+    np.testing.assert_equal(pairs, want['pairs'][:1000])
+
+
+def test_wide_count_and_write_entry_points(cuda_env, oracle):
+    """col_traverse_wide_count / _write over query sub-ranges (the multi-GPU sharding primitives)."""
+    import torch
+    from collision_b200 import _lib
+    from collision_b200.collision import Collider
+    dev, cq = cuda_env
+    n = 4000
+    c, r = G.random_spheres(n)
+    want = oracle.collide(c, r)
+    col = Collider(dev, n, 8, 64)
+    run_collider(cuda_env, col, c, r, 0, np.dtype('float32'))
+    L, P, S = _lib.lib(), _lib.ptr, cq.cuda_stream
+    bounds = [0, 1000, 1001, 2500, n]
+    rows = []
+    for qb, qe in zip(bounds, bounds[1:]):
+        counts = dev_empty((qe - qb) * 4)
+        tot = torch.zeros(1, dtype=torch.int64, device=dev)
+        assert L.col_traverse_wide_count(P(tot), P(counts), P(col._wide_buf), P(col._bounds_buf), 0, n, qb, qe, S) == 0
+        cq.synchronize()
+        cnt = to_host(counts, 'uint32', (qe - qb,))
+        np.testing.assert_equal(cnt, want['counts'][qb:qe])
+        assert int(tot.item()) == int(cnt.sum())
+        offs = to_dev(oracle.exclusive_scan(cnt))
+        out = dev_empty(max(int(cnt.sum()), 1) * 8)
+        assert L.col_traverse_wide_write(P(out), int(cnt.sum()), P(offs), 0, P(col._wide_buf), P(col._bounds_buf),
+                                         P(col._ids_bufs[1]), 0, n, qb, qe, S) == 0
+        cq.synchronize()
+        rows.append(to_host(out, 'uint32', (int(cnt.sum()), 2)))
+        # fused over the same sub-range gives the same rows
+        out2 = dev_empty(max(int(cnt.sum()), 1) * 8)
+        scr = dev_empty(L.col_traverse_scratch_bytes(qe - qb))
+        assert L.col_traverse_wide_fused(P(out2), int(cnt.sum()), 0, P(tot), P(col._wide_buf), P(col._bounds_buf),
+                                         P(col._ids_bufs[1]), 0, n, qb, qe, P(scr), S) == 0
+        cq.synchronize()
+        np.testing.assert_equal(to_host(out2, 'uint32', (int(cnt.sum()), 2)), rows[-1])
+        assert int(tot.item()) == int(cnt.sum())
+    np.testing.assert_equal(np.concatenate(rows), want['pairs'])
