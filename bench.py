@@ -175,7 +175,7 @@ STAGE_BYTES = {   # algorithmic bytes per launch (SURVEY.md 8(d) / DESIGN.md), n
     "traverse_count": lambda n, m: 36 * n,
     "scan": lambda n, m: 8 * n,
     "traverse_write": lambda n, m: 36 * n + 8 * m,
-    "traverse_fused": lambda n, m: 36 * n + 8 * m,
+    "traverse_pairs": lambda n, m: 44 * n + 8 * m,   # traversal 36n + compaction 8n + 8m
 }
 
 
@@ -224,18 +224,26 @@ def run_ours(args):
     pairs_pin = torch.empty(max(local_cap, 1) * 2, dtype=torch.int32).pin_memory()
     n_pin = torch.zeros(1, dtype=torch.int32).pin_memory()
 
+    kw = {"sync_totals": False} if world > 1 else {}
+
     def step():
-        return collider.get_collisions(cq, coords_d, radii_d, n_buf, pairs_d, local_cap)
+        return collider.get_collisions(cq, coords_d, radii_d, n_buf, pairs_d, local_cap, **kw)
 
-    for _ in range(max(args.warmup, 3)):
-        flush.fill_(0)
-        step()
-    barrier()
-
-    # ---- device-resident timing: K steps, one event pair per step, L2 flushed in between
+    # clocks are sampled from the warm-up through the timed region (the timed region
+    # alone lasts ~20 ms, shorter than nvidia-smi's sampling period)
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
+    t_warm = time.perf_counter()
+    i = 0
+    while i < max(args.warmup, 3) or time.perf_counter() - t_warm < 0.5:
+        flush.fill_(0)
+        step()
+        torch.cuda.synchronize()
+        i += 1
+    barrier()
+
+    # ---- device-resident timing: K steps, one event pair per step, L2 flushed in between
     collider.stage_events = []
     launches0 = collider.kernel_launches
     step_events = []
@@ -271,7 +279,7 @@ def run_ours(args):
         with torch.cuda.stream(cq):
             coords_d.copy_(coords_pin, non_blocking=True)
             radii_d.copy_(radii_pin, non_blocking=True)
-            collider.get_collisions(cq, coords_d, radii_d, n_buf, pairs_d, local_cap)
+            collider.get_collisions(cq, coords_d, radii_d, n_buf, pairs_d, local_cap, **kw)
             n_pin.copy_(n_buf, non_blocking=True)
         cq.synchronize()
         got = collider.local_pairs if world > 1 else (int(n_pin.item()) & 0xFFFFFFFF)

@@ -184,24 +184,10 @@ class Collider:
                        n_collisions, wait_for=None):
         if collisions_buf is None and n_collisions > 0:
             raise ValueError("Invalid collisions_buf for n_collisions > 0")
-        L, P, S = _lib.lib(), _lib.ptr, _lib.stream_ptr(cq)
-        n, code = self.size, self.program._code
         self._ensure_scratch()
         _lib.begin(cq, wait_for)
-        mark = self._mark
-        mark(cq, "begin", 0)
-
-        _lib.check(L.col_bounds(P(coords_buf), n, code, 4, P(self._bounds_buf), P(self.reducer._ensure_scratch()), S),
-                   "col_bounds")
-        mark(cq, "bounds", 1)
-        _lib.check(L.col_morton(P(self._codes_bufs[0]), P(self._ids_bufs[0]), P(coords_buf), P(self._bounds_buf),
-                                code, n, n, S), "col_morton")
-        mark(cq, "morton", 1)
-        # padding keys are not needed by this sort: only the n real keys move
-        _lib.check(L.col_sort_pairs(P(self._codes_bufs[0]), P(self._codes_bufs[1]), P(self._ids_bufs[0]),
-                                    P(self._ids_bufs[1]), n, 4, 4, MORTON_BITS, P(self.sorter._ensure_scratch()), S),
-                   "col_sort_pairs")
-        mark(cq, "sort", 2 + (MORTON_BITS + 7) // 8)   # histogram + digit bases + one launch per digit
+        self._mark(cq, "begin", 0)
+        self._sort_stage(cq, coords_buf)
         if self.fast:
             self._traverse_fast(cq, coords_buf, radii_buf, n_collisions_buf, collisions_buf, n_collisions)
         else:
@@ -215,9 +201,24 @@ class Collider:
             ev.record(cq)
             self.stage_events.append((name, ev))
 
-    def _traverse_fast(self, cq, coords_buf, radii_buf, n_collisions_buf, collisions_buf, n_collisions):
-        """Tree + refit emitting the traversal records, then ONE launch that walks
-        every query once and commits its rows in the deterministic order."""
+    def _sort_stage(self, cq, coords_buf):
+        """scene bounds -> Morton codes + ids -> stable sort (collision.py:157-169 upstream)."""
+        L, P, S = _lib.lib(), _lib.ptr, _lib.stream_ptr(cq)
+        n, code, mark = self.size, self.program._code, self._mark
+        _lib.check(L.col_bounds(P(coords_buf), n, code, 4, P(self._bounds_buf), P(self.reducer._ensure_scratch()), S),
+                   "col_bounds")
+        mark(cq, "bounds", 1)
+        _lib.check(L.col_morton(P(self._codes_bufs[0]), P(self._ids_bufs[0]), P(coords_buf), P(self._bounds_buf),
+                                code, n, n, S), "col_morton")
+        mark(cq, "morton", 1)
+        # padding keys are not needed by this sort: only the n real keys move
+        _lib.check(L.col_sort_pairs(P(self._codes_bufs[0]), P(self._codes_bufs[1]), P(self._ids_bufs[0]),
+                                    P(self._ids_bufs[1]), n, 4, 4, MORTON_BITS, P(self.sorter._ensure_scratch()), S),
+                   "col_sort_pairs")
+        mark(cq, "sort", 2 + (MORTON_BITS + 7) // 8)   # histogram + digit bases + one launch per digit
+
+    def _build_wide(self, cq, coords_buf, radii_buf):
+        """Karras tree + leaf boxes + refit, emitting the traversal records."""
         L, P, S = _lib.lib(), _lib.ptr, _lib.stream_ptr(cq)
         n, code, mark = self.size, self.program._code, self._mark
         _lib.check(L.col_build_tree_wide(P(self._codes_bufs[1]), P(self._ids_bufs[1]), P(self._nodes_buf),
@@ -226,12 +227,24 @@ class Collider:
         _lib.check(L.col_refit_wide(P(self._bounds_buf), P(self._wide_buf), P(self._flags_buf), P(self._nodes_buf),
                                     P(coords_buf), P(radii_buf), code, n, S), "col_refit_wide")
         mark(cq, "refit", 1)
-        _lib.check(L.col_traverse_wide_fused(P(collisions_buf), n_collisions, 0, P(self._total_buf),
-                                             P(self._wide_buf), P(self._bounds_buf), P(self._ids_bufs[1]), code,
-                                             n, 0, n, P(self._trv_scratch), S), "col_traverse_wide_fused")
+
+    def _walk_range(self, cq, collisions_buf, n_collisions, q_begin, q_end, base=0):
+        """Queries [q_begin, q_end) (sorted positions): every query walks once (hits
+        parked), the counts are scanned, the rows are emitted in the deterministic
+        order.  Leaves the u64 row count of the range in self._total_buf."""
+        L, P, S = _lib.lib(), _lib.ptr, _lib.stream_ptr(cq)
+        _lib.check(L.col_traverse_wide_pairs(P(collisions_buf), n_collisions, base, P(self._total_buf),
+                                             P(self._wide_buf), P(self._bounds_buf), P(self._ids_bufs[1]),
+                                             self.program._code, self.size, q_begin, q_end,
+                                             P(self._trv_scratch), S), "col_traverse_wide_pairs")
+        self._mark(cq, "traverse_pairs" if n_collisions else "traverse_count", 3 if n_collisions else 1)
+
+    def _traverse_fast(self, cq, coords_buf, radii_buf, n_collisions_buf, collisions_buf, n_collisions):
+        self._build_wide(cq, coords_buf, radii_buf)
+        self._walk_range(cq, collisions_buf, n_collisions, 0, self.size)
         # counter = true total (low 32 bits, as upstream's uint counter)
-        _lib.check(L.col_copy(P(n_collisions_buf), P(self._total_buf), 4, S), "col_copy")
-        mark(cq, "traverse_fused" if n_collisions else "traverse_count", 1)
+        _lib.check(_lib.lib().col_copy(_lib.ptr(n_collisions_buf), _lib.ptr(self._total_buf), 4,
+                                       _lib.stream_ptr(cq)), "col_copy")
 
     def _traverse_reference_layout(self, cq, coords_buf, radii_buf, n_collisions_buf, collisions_buf, n_collisions):
         """The same stages on the reference's Node / Bound arrays only (kernel-level

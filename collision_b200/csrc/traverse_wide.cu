@@ -8,22 +8,21 @@
 //    children's boxes, indices and right edges (written by tree.cu + refit.cu):
 //    a visit is two 256-bit loads from one line instead of seven 128-bit loads
 //    from five lines (the profile of the Node/Bound walk is L1-sector bound).
-//  * count -> scan -> write needs no second walk and no scan launch: a block of
-//    128 consecutive queries walks once, each thread parks up to STASH hits in
-//    shared memory, the block scans its counts, chains its total to the
-//    preceding blocks by decoupled look-back ({flag:2, total:62} words, blocks
-//    ordered by an atomic ticket) and writes its rows at the resulting offsets.
-//    The row order is exactly that of the reference's work-items run
-//    sequentially (query-major, DFS order, child a before b).  Queries with
-//    more than STASH hits walk a second time for the remainder only.
+//  * count -> scan -> write without a second walk: every query walks once and
+//    parks its first TRV_STASH hits in a k-major global array (coalesced rows, only
+//    the used ones move); the counts are scanned by the single-pass scan kernel;
+//    an emit kernel copies the parked hits to their final rows.  The row order is
+//    exactly that of the reference's work-items run sequentially (query-major,
+//    DFS order, child a before b).  Only queries with more than TRV_STASH hits walk
+//    a second time, for the remainder.  (A single fused kernel chaining blocks by
+//    decoupled look-back was measured slower: blocks of dense regions stall every
+//    later block, and a shared-memory stash shrinks the L1 the walk depends on.)
 #include "common.cuh"
 
 namespace {
 
 constexpr int TRV_THREADS = 128;
 constexpr int TRV_STASH = 32;
-constexpr size_t TRV_STATUS_OFF = 256;
-constexpr uint64_t TRV_PARTIAL = 1ull << 62, TRV_INCLUSIVE = 2ull << 62, TRV_VALUE = (1ull << 62) - 1;
 
 template <typename T> struct WNode {
     T a[6], b[6];
@@ -132,95 +131,73 @@ count_kernel(unsigned long long* __restrict__ total, uint32_t* __restrict__ coun
     }
 }
 
-// ---- fused walk + compaction -------------------------------------------------
+// ---- walk once: per-query counts + parked hits ---------------------------------
+// Every query walks ONCE.  Its hit count goes to counts[], its first TRV_STASH hits
+// (sorted leaf positions) are parked in a k-major global array stash[k * nq + i]:
+// lanes of a warp park their k-th hit in one 128-byte row, and only rows that
+// are actually used ever move.  No inter-block dependency, so dense and sparse
+// regions of the scene do not stall each other.
 template <typename T>
 __global__ void __launch_bounds__(TRV_THREADS)
-fused_kernel(uint32_t* __restrict__ pairs, uint64_t capacity, uint64_t base, unsigned long long* __restrict__ total_out,
-             const T* __restrict__ wide, const T* __restrict__ bounds, const uint32_t* __restrict__ ids, uint32_t n,
-             uint32_t q_begin, uint32_t q_end, unsigned* ticket, uint64_t* status) {
-    __shared__ uint32_t s_stash[TRV_STASH * TRV_THREADS];
-    __shared__ uint32_t s_warp[TRV_THREADS / 32];
-    __shared__ unsigned s_tile;
-    __shared__ uint64_t s_prefix;
-
-    if (threadIdx.x == 0) s_tile = atomicAdd(ticket, 1u);
-    __syncthreads();
-    const unsigned tile = s_tile;
-    const uint32_t q = q_begin + tile * TRV_THREADS + threadIdx.x;
+walk_park_kernel(unsigned long long* __restrict__ total, uint32_t* __restrict__ counts, uint32_t* __restrict__ stash,
+                 const T* __restrict__ wide, const T* __restrict__ bounds, uint32_t n, uint32_t q_begin,
+                 uint32_t q_end) {
+    const uint32_t i = blockIdx.x * TRV_THREADS + threadIdx.x;
+    const uint32_t q = q_begin + i;
+    const uint32_t nq = q_end - q_begin;
     const uint32_t leaf_start = n - 1;
-    const bool live = q < q_end;
-    const unsigned lane = lane_id(), warp = threadIdx.x >> 5;
-
-    Query<T> query;
     uint32_t hits = 0;
-    if (live) {
-        query = load_query(bounds, leaf_start + q);
-        uint32_t* stash = s_stash + threadIdx.x;
-        hits = walk(wide, query, q, leaf_start, [stash](uint32_t pos, uint32_t k) {
-            if (k < TRV_STASH) stash[k * TRV_THREADS] = pos;
+    if (q < q_end) {
+        const Query<T> query = load_query(bounds, leaf_start + q);
+        uint32_t* park = stash + i;
+        hits = walk(wide, query, q, leaf_start, [park, nq](uint32_t pos, uint32_t k) {
+            if (k < TRV_STASH) park[(size_t)k * nq] = pos;
         });
+        counts[i] = hits;
     }
-
-    // block exclusive scan of the hit counts
-    uint32_t inc = hits;
+    __shared__ uint32_t s_sum[TRV_THREADS / 32];
+    uint32_t v = hits;
 #pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-        const uint32_t up = __shfl_up_sync(0xffffffffu, inc, o);
-        if (lane >= o) inc += up;
-    }
-    if (lane == 31) s_warp[warp] = inc;
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if (lane_id() == 0) s_sum[threadIdx.x >> 5] = v;
     __syncthreads();
-    uint32_t local = inc - hits, tile_total = 0;
-#pragma unroll
-    for (int w = 0; w < TRV_THREADS / 32; w++) {
-        const uint32_t t = s_warp[w];
-        if (w < (int)warp) local += t;
-        tile_total += t;
+    if (threadIdx.x == 0) {
+        unsigned long long t = 0;
+        for (int w = 0; w < TRV_THREADS / 32; w++) t += s_sum[w];
+        if (t) atomicAdd(total, t);
     }
+}
 
-    // decoupled look-back over the preceding tiles (warp 0, 32 tiles per step)
-    if (warp == 0) {
-        uint64_t prefix = 0;
-        if (tile == 0) {
-            if (lane == 0) st_relaxed_u64(status, TRV_INCLUSIVE | tile_total);
-        } else {
-            if (lane == 0) st_relaxed_u64(status + tile, TRV_PARTIAL | tile_total);
-            int64_t look = (int64_t)tile - 1 - lane;
-            while (true) {
-                uint64_t st = TRV_INCLUSIVE;
-                if (look >= 0) {
-                    do { st = ld_relaxed_u64(status + look); } while ((st >> 62) == 0);
-                }
-                const unsigned inc_mask = __ballot_sync(0xffffffffu, (st >> 62) == 2);
-                const unsigned first = inc_mask ? (unsigned)__ffs(inc_mask) - 1 : 31u;
-                uint64_t c = (lane <= first) ? (st & TRV_VALUE) : 0;
-#pragma unroll
-                for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
-                prefix += c;
-                if (inc_mask) break;
-                look -= 32;
-            }
-            if (lane == 0) st_relaxed_u64(status + tile, TRV_INCLUSIVE | ((prefix + tile_total) & TRV_VALUE));
-        }
-        if (lane == 0) {
-            s_prefix = prefix;
-            if (total_out && (uint64_t)(tile + 1) * TRV_THREADS >= (uint64_t)(q_end - q_begin))
-                *total_out = prefix + tile_total;
-        }
-    }
-    __syncthreads();
-    if (!live || hits == 0) return;
-
-    const uint64_t out = base + s_prefix + local;
-    if (out >= capacity) return;
+// ---- emit: rows to their final, deterministic positions -----------------------
+// offsets = exclusive scan of counts.  Row k of query i lands at base + offsets[i] + k
+// (query-major, DFS order: the order of the reference's work-items run sequentially).
+// Parked hits are simply copied (ids gathered); a query with more than TRV_STASH hits
+// walks again for the remainder only.
+template <typename T>
+__global__ void __launch_bounds__(TRV_THREADS)
+emit_kernel(uint32_t* __restrict__ pairs, uint64_t capacity, uint64_t base, const uint32_t* __restrict__ offsets,
+            const unsigned long long* __restrict__ total, const uint32_t* __restrict__ stash,
+            const T* __restrict__ wide, const T* __restrict__ bounds, const uint32_t* __restrict__ ids, uint32_t n,
+            uint32_t q_begin, uint32_t q_end) {
+    const uint32_t i = blockIdx.x * TRV_THREADS + threadIdx.x;
+    const uint32_t q = q_begin + i;
+    if (q >= q_end) return;
+    const uint32_t nq = q_end - q_begin;
+    const uint32_t off = offsets[i];
+    const uint32_t next = (i + 1 < nq) ? offsets[i + 1] : (uint32_t)*total;
+    const uint32_t hits = next - off;
+    const uint64_t out = base + off;
+    if (hits == 0 || out >= capacity) return;
     const uint32_t qid = __ldg(ids + q);
     const uint32_t parked = min(hits, (uint32_t)TRV_STASH);
     for (uint32_t k = 0; k < parked; k++) {
         const uint64_t at = out + k;
         if (at < capacity)
-            *reinterpret_cast<uint2*>(pairs + at * 2) = make_uint2(qid, __ldg(ids + s_stash[k * TRV_THREADS + threadIdx.x]));
+            *reinterpret_cast<uint2*>(pairs + at * 2) = make_uint2(qid, __ldg(ids + __ldg(stash + (size_t)k * nq + i)));
     }
-    if (hits > TRV_STASH) {  // rare: walk again for the rows that did not fit the stash
+    if (hits > TRV_STASH) {
+        const uint32_t leaf_start = n - 1;
+        const Query<T> query = load_query(bounds, leaf_start + q);
         walk(wide, query, q, leaf_start, [=](uint32_t pos, uint32_t k) {
             const uint64_t at = out + k;
             if (k >= TRV_STASH && at < capacity)
@@ -252,10 +229,19 @@ inline bool bad_range(uint32_t n, uint32_t q_begin, uint32_t q_end) { return q_e
 
 }  // namespace
 
-COL_API size_t col_traverse_scratch_bytes(uint32_t n_queries) {
-    const size_t tiles = ((size_t)n_queries + TRV_THREADS - 1) / TRV_THREADS;
-    return TRV_STATUS_OFF + (tiles ? tiles : 1) * sizeof(uint64_t);
+// scratch of col_traverse_wide_pairs: [counts/offsets: nq u32][scan scratch][stash: TRV_STASH x nq u32]
+struct PairsLayout { size_t counts, scan, stash, total; };
+static PairsLayout pairs_layout(uint32_t nq) {
+    auto up = [](size_t x) { return (x + 255) & ~(size_t)255; };
+    PairsLayout L;
+    L.counts = 0;
+    L.scan = up((size_t)nq * 4 + 4);
+    L.stash = L.scan + up(col_scan_scratch_bytes(nq));
+    L.total = L.stash + up((size_t)nq * 4 * TRV_STASH);
+    return L;
 }
+
+COL_API size_t col_traverse_scratch_bytes(uint32_t n_queries) { return pairs_layout(n_queries ? n_queries : 1).total; }
 
 COL_API int col_traverse_wide_count(uint64_t* total, uint32_t* counts, const void* wide, const void* bounds, int dtype,
                                     uint32_t n, uint32_t q_begin, uint32_t q_end, void* stream) {
@@ -275,24 +261,34 @@ COL_API int col_traverse_wide_count(uint64_t* total, uint32_t* counts, const voi
     return 0;
 }
 
-COL_API int col_traverse_wide_fused(uint32_t* pairs, uint64_t capacity, uint64_t base, uint64_t* total_out,
+COL_API int col_traverse_wide_pairs(uint32_t* pairs, uint64_t capacity, uint64_t base, uint64_t* total_out,
                                     const void* wide, const void* bounds, const uint32_t* ids_sorted, int dtype,
                                     uint32_t n, uint32_t q_begin, uint32_t q_end, void* scratch, void* stream) {
-    if (!wide || !bounds || !ids_sorted || !scratch || bad_range(n, q_begin, q_end) || (!pairs && capacity))
+    if (!wide || !bounds || !ids_sorted || !scratch || !total_out || bad_range(n, q_begin, q_end) || (!pairs && capacity))
         return COL_ERR_BAD_ARG;
+    if (dtype != COL_F32 && dtype != COL_F64) return COL_ERR_UNSUPPORTED;
     if (capacity == 0) return col_traverse_wide_count(total_out, nullptr, wide, bounds, dtype, n, q_begin, q_end, stream);
     cudaStream_t s = col_stream(stream);
-    if (q_begin == q_end || n < 2) return total_out ? (int)cudaMemsetAsync(total_out, 0, sizeof(uint64_t), s) : 0;
-    COL_CUDA(cudaMemsetAsync(scratch, 0, col_traverse_scratch_bytes(q_end - q_begin), s));
-    unsigned* ticket = reinterpret_cast<unsigned*>(scratch);
-    uint64_t* status = reinterpret_cast<uint64_t*>(reinterpret_cast<char*>(scratch) + TRV_STATUS_OFF);
-    const unsigned blocks = col_blocks(q_end - q_begin, TRV_THREADS);
+    COL_CUDA(cudaMemsetAsync(total_out, 0, sizeof(uint64_t), s));
+    if (q_begin == q_end || n < 2) return 0;
+    const uint32_t nq = q_end - q_begin;
+    const PairsLayout L = pairs_layout(nq);
+    char* sc = reinterpret_cast<char*>(scratch);
+    uint32_t* counts = reinterpret_cast<uint32_t*>(sc + L.counts);
+    uint32_t* stash = reinterpret_cast<uint32_t*>(sc + L.stash);
+    unsigned long long* total = reinterpret_cast<unsigned long long*>(total_out);
+    const unsigned blocks = col_blocks(nq, TRV_THREADS);
     if (dtype == COL_F32)
-        fused_kernel<float><<<blocks, TRV_THREADS, 0, s>>>(pairs, capacity, base, (unsigned long long*)total_out, (const float*)wide, (const float*)bounds, ids_sorted, n, q_begin, q_end, ticket, status);
-    else if (dtype == COL_F64)
-        fused_kernel<double><<<blocks, TRV_THREADS, 0, s>>>(pairs, capacity, base, (unsigned long long*)total_out, (const double*)wide, (const double*)bounds, ids_sorted, n, q_begin, q_end, ticket, status);
+        walk_park_kernel<float><<<blocks, TRV_THREADS, 0, s>>>(total, counts, stash, (const float*)wide, (const float*)bounds, n, q_begin, q_end);
     else
-        return COL_ERR_UNSUPPORTED;
+        walk_park_kernel<double><<<blocks, TRV_THREADS, 0, s>>>(total, counts, stash, (const double*)wide, (const double*)bounds, n, q_begin, q_end);
+    COL_CHECK_LAUNCH();
+    const int rc = col_exclusive_scan_u32(counts, nq, nullptr, sc + L.scan, stream);
+    if (rc) return rc;
+    if (dtype == COL_F32)
+        emit_kernel<float><<<blocks, TRV_THREADS, 0, s>>>(pairs, capacity, base, counts, total, stash, (const float*)wide, (const float*)bounds, ids_sorted, n, q_begin, q_end);
+    else
+        emit_kernel<double><<<blocks, TRV_THREADS, 0, s>>>(pairs, capacity, base, counts, total, stash, (const double*)wide, (const double*)bounds, ids_sorted, n, q_begin, q_end);
     COL_CHECK_LAUNCH();
     return 0;
 }

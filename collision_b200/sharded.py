@@ -1,0 +1,116 @@
+"""Traversal sharded over the GPUs of one box (one process per GPU, torch.distributed).
+
+The reference is single-device.  This is the multi-GPU form BASELINE.json's
+north_star prescribes: the scene is sorted, built and refitted ONCE (rank 0), the
+read-only traversal data is broadcast over NVLink (NCCL), every rank walks a
+contiguous range of the Morton-sorted queries and keeps its rows, and the per-rank
+row totals are all-gathered so every rank knows the global count and its base
+offset.  Concatenating the ranks' lists in rank order gives exactly the 1-GPU
+(= sequential reference) list.
+
+What travels (per sphere): the traversal record 64 B + the leaf box 32 B + the
+sorted id 4 B = 100 B (f32); the Node array stays on rank 0.
+
+The distributed plumbing (`shard_range`, `exchange_totals`, `broadcast_buffers`)
+is device-agnostic so that it is covered by world_size-2 gloo tests on CPU.
+"""
+import torch
+import torch.distributed as dist
+from numpy import dtype
+
+from . import _lib
+from .collision import Collider
+
+
+def shard_range(n, world, rank):
+    """Contiguous range of sorted query positions owned by `rank`: [n*r/k, n*(r+1)/k)."""
+    return (n * rank) // world, (n * (rank + 1)) // world
+
+
+def exchange_totals(local_total, group=None):
+    """all_gather of the per-rank row counts.  `local_total`: 1-element int64 tensor on
+    the group's device.  Returns the (world,) int64 tensor of totals (same device);
+    rank r's base offset is totals[:r].sum() and the global count totals.sum()."""
+    world = dist.get_world_size(group)
+    out = torch.empty(world, dtype=torch.int64, device=local_total.device)
+    dist.all_gather_into_tensor(out, local_total.reshape(1), group=group)
+    return out
+
+
+def broadcast_buffers(buffers, src=0, group=None):
+    """Broadcast each (uint8) buffer from `src`; over NCCL this rides NVLink / NVSwitch."""
+    for b in buffers:
+        dist.broadcast(b, src=src, group=group)
+
+
+class ShardedCollider:
+    """Collider.get_collisions across `world` GPUs.  Same call signature; rank 0 must
+    pass the scene (`coords_buf`, `radii_buf`), the other ranks may pass None.
+
+    After a call: `n_collisions_buf[0]` = global row count (low 32 bits, like the
+    reference's counter) on every rank, `collisions_buf` = this rank's rows
+    (`local_pairs` of them, global row index `pair_base` + i)."""
+
+    def __init__(self, ctx, size, ngroups, group_size, coord_dtype=dtype('float32'), group=None, src=0):
+        self.collider = Collider(ctx, size, ngroups, group_size, coord_dtype)
+        self.group = group
+        self.src = src
+        self.world = dist.get_world_size(group)
+        self.rank = dist.get_rank(group)
+        self.size = size
+        self.q_begin, self.q_end = shard_range(size, self.world, self.rank)
+        self.local_pairs = 0
+        self.pair_base = 0
+        self.total_pairs = 0
+        self._totals = None
+
+    # instrumentation is the inner collider's
+    @property
+    def stage_events(self):
+        return self.collider.stage_events
+
+    @stage_events.setter
+    def stage_events(self, v):
+        self.collider.stage_events = v
+
+    @property
+    def kernel_launches(self):
+        return self.collider.kernel_launches
+
+    def _shared_buffers(self):
+        c = self.collider
+        n = c.size
+        isz = c.program.coord_dtype.itemsize
+        leaf_boxes = c._bounds_buf[(n - 1) * 8 * isz:(2 * n - 1) * 8 * isz]
+        return [c._wide_buf, leaf_boxes, c._ids_bufs[1][:n * 4]]
+
+    def get_collisions(self, cq, coords_buf, radii_buf, n_collisions_buf, collisions_buf, n_collisions,
+                       wait_for=None, sync_totals=True):
+        """n_collisions: capacity (rows) of THIS rank's collisions_buf."""
+        if collisions_buf is None and n_collisions > 0:
+            raise ValueError("Invalid collisions_buf for n_collisions > 0")
+        c = self.collider
+        c._ensure_scratch()
+        _lib.begin(cq, wait_for)
+        c._mark(cq, "begin", 0)
+        with torch.cuda.stream(cq):
+            if self.rank == self.src:
+                c._sort_stage(cq, coords_buf)
+                c._build_wide(cq, coords_buf, radii_buf)
+            broadcast_buffers(self._shared_buffers(), self.src, self.group)
+            c._mark(cq, "broadcast", 0)
+            c._walk_range(cq, collisions_buf, n_collisions, self.q_begin, self.q_end)
+            self._totals = exchange_totals(c._total_buf, self.group)
+            total = self._totals.sum().reshape(1)
+            _lib.check(_lib.lib().col_copy(_lib.ptr(n_collisions_buf), _lib.ptr(total), 4, _lib.stream_ptr(cq)),
+                       "col_copy")
+            total.record_stream(cq)
+            c._mark(cq, "all_gather", 0)
+        ev = _lib.done(cq)
+        if sync_totals:     # host-visible bookkeeping (one small readback)
+            ev.synchronize()
+            t = self._totals.tolist()
+            self.local_pairs = t[self.rank]
+            self.pair_base = sum(t[:self.rank])
+            self.total_pairs = sum(t)
+        return ev

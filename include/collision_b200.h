@@ -168,11 +168,12 @@ int col_traverse_atomic(uint32_t* pairs, uint32_t* counter, uint32_t capacity, c
  * the traversal reads only its leaf part (the query boxes).  The arithmetic and
  * the reported rows are identical to the entry points above.
  *
- * col_traverse_wide_fused: one walk per query + deterministic compaction in ONE
- * launch (decoupled look-back over blocks of 128 queries): row k of query q
+ * col_traverse_wide_pairs: one walk per query + deterministic compaction (walk
+ * and park hits -> single-pass scan of the counts -> emit): row k of query q
  * lands at base + (number of rows of queries q_begin..q-1) + k when that index
- * is < capacity; *total_out (u64, may be NULL) = rows found in the range.
- * capacity == 0: count only.  ids_sorted: ids in sorted order (the sort's
+ * is < capacity; *total_out (u64, required) = rows found in the range (the list
+ * positions are exact for totals < 2^32 per call).  capacity == 0: count only.
+ * scratch: col_traverse_scratch_bytes(q_end - q_begin).  ids_sorted: ids in sorted order (the sort's
  * payload output). */
 int col_build_tree_wide(const uint32_t* codes_sorted, const uint32_t* ids_sorted, void* nodes, void* wide,
                         int dtype, uint32_t n, void* stream);
@@ -181,7 +182,7 @@ int col_refit_wide(void* bounds, void* wide, uint32_t* flags, const void* nodes,
 size_t col_traverse_scratch_bytes(uint32_t n_queries);
 int col_traverse_wide_count(uint64_t* total, uint32_t* counts, const void* wide, const void* bounds, int dtype,
                             uint32_t n, uint32_t q_begin, uint32_t q_end, void* stream);
-int col_traverse_wide_fused(uint32_t* pairs, uint64_t capacity, uint64_t base, uint64_t* total_out,
+int col_traverse_wide_pairs(uint32_t* pairs, uint64_t capacity, uint64_t base, uint64_t* total_out,
                             const void* wide, const void* bounds, const uint32_t* ids_sorted, int dtype,
                             uint32_t n, uint32_t q_begin, uint32_t q_end, void* scratch, void* stream);
 int col_traverse_wide_write(uint32_t* pairs, uint64_t capacity, const uint32_t* offsets, uint64_t base,
