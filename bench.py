@@ -193,7 +193,8 @@ def run_ours(args):
     dev = torch.device("cuda", local_rank)
     torch.cuda.set_device(dev)
     if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
+        import datetime
+        dist.init_process_group("nccl", device_id=dev, timeout=datetime.timedelta(seconds=120))
     _lib.lib()   # fail loudly if the sm_100a library is missing
 
     def barrier():
@@ -213,7 +214,7 @@ def run_ours(args):
         collider = Collider(dev, n, 8, 128)
     else:
         from collision_b200.sharded import ShardedCollider
-        collider = ShardedCollider(dev, n, 8, 128)
+        collider = ShardedCollider(dev, n, 8, 128, mode=args.multi_gpu_mode)
     n_buf = torch.zeros(1, dtype=torch.int32, device=dev)
 
     # size the pair buffer from a count-only call (the reference's own protocol)
@@ -236,7 +237,8 @@ def run_ours(args):
         sampler.start()
     t_warm = time.perf_counter()
     i = 0
-    while i < max(args.warmup, 3) or time.perf_counter() - t_warm < 0.5:
+    # (time-based extension only on a single rank: ranks must issue identical collective sequences)
+    while i < max(args.warmup, 3) or (world == 1 and time.perf_counter() - t_warm < 0.5):
         flush.fill_(0)
         step()
         torch.cuda.synchronize()
@@ -299,7 +301,8 @@ def run_ours(args):
 
     if rank == 0:
         peak, peak_src = measured_hbm_peak()
-        dom = max(stage_ms, key=stage_ms.get) if stage_ms else None
+        kernels_only = {k: v for k, v in stage_ms.items() if k in STAGE_BYTES}
+        dom = max(kernels_only, key=kernels_only.get) if kernels_only else None
         roofline = None
         if dom:
             q = n // world if dom.startswith("traverse") else n
@@ -325,8 +328,8 @@ def run_ours(args):
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic",
             "config": workload_config(n, {"parallelism": "single GPU" if world == 1 else
-                                          "tree built on rank 0, NCCL broadcast, traversal sharded over {} "
-                                          "Morton ranges".format(world)}),
+                                          "{}: traversal sharded over {} contiguous Morton ranges, NCCL "
+                                          "broadcast + all_gather of row totals".format(args.multi_gpu_mode, world)}),
             "pairs": total, "pairs_per_sec": total / (ms_per_step * 1e-3),
             "e2e": {"value": n / e2e_sec, "unit": UNIT,
                     "h2d_bytes_per_step": coords_pin.numel() * 4 + radii_pin.numel() * 4,
@@ -347,6 +350,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
+    ap.add_argument("--multi-gpu-mode", choices=["broadcast_tree", "replicate_build"], default="replicate_build",
+                    help="N>1: broadcast the tree built on rank 0 (north_star) or the inputs and build everywhere")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -44,14 +44,27 @@ def broadcast_buffers(buffers, src=0, group=None):
 
 
 class ShardedCollider:
-    """Collider.get_collisions across `world` GPUs.  Same call signature; rank 0 must
-    pass the scene (`coords_buf`, `radii_buf`), the other ranks may pass None.
+    """Collider.get_collisions across `world` GPUs.  Same call signature; rank `src`
+    passes the scene (`coords_buf`, `radii_buf`); in mode "broadcast_tree" the other
+    ranks may pass None, in mode "replicate_build" they pass buffers to receive it.
 
     After a call: `n_collisions_buf[0]` = global row count (low 32 bits, like the
     reference's counter) on every rank, `collisions_buf` = this rank's rows
     (`local_pairs` of them, global row index `pair_base` + i)."""
 
-    def __init__(self, ctx, size, ngroups, group_size, coord_dtype=dtype('float32'), group=None, src=0):
+    MODES = ("broadcast_tree", "replicate_build")
+
+    def __init__(self, ctx, size, ngroups, group_size, coord_dtype=dtype('float32'), group=None, src=0,
+                 mode="broadcast_tree"):
+        """mode "broadcast_tree" (north_star): rank `src` sorts, builds and refits; the
+        traversal data (100 B per sphere) is broadcast.
+        mode "replicate_build": the INPUT (coords + radii, 20 B per sphere) is broadcast
+        from `src` and every rank builds the identical tree itself -- the build is
+        deterministic and bit-exact, so the result is the same; it trades redundant
+        compute for 5x less NVLink traffic and no serial rank-0 phase."""
+        if mode not in self.MODES:
+            raise ValueError("mode must be one of {}".format(self.MODES))
+        self.mode = mode
         self.collider = Collider(ctx, size, ngroups, group_size, coord_dtype)
         self.group = group
         self.src = src
@@ -94,11 +107,17 @@ class ShardedCollider:
         _lib.begin(cq, wait_for)
         c._mark(cq, "begin", 0)
         with torch.cuda.stream(cq):
-            if self.rank == self.src:
+            if self.mode == "broadcast_tree":
+                if self.rank == self.src:
+                    c._sort_stage(cq, coords_buf)
+                    c._build_wide(cq, coords_buf, radii_buf)
+                broadcast_buffers(self._shared_buffers(), self.src, self.group)
+                c._mark(cq, "broadcast", 0)
+            else:
+                broadcast_buffers([coords_buf, radii_buf], self.src, self.group)
+                c._mark(cq, "broadcast", 0)
                 c._sort_stage(cq, coords_buf)
                 c._build_wide(cq, coords_buf, radii_buf)
-            broadcast_buffers(self._shared_buffers(), self.src, self.group)
-            c._mark(cq, "broadcast", 0)
             c._walk_range(cq, collisions_buf, n_collisions, self.q_begin, self.q_end)
             self._totals = exchange_totals(c._total_buf, self.group)
             total = self._totals.sum().reshape(1)
