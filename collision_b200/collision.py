@@ -222,7 +222,7 @@ class Collider:
         L, P, S = _lib.lib(), _lib.ptr, _lib.stream_ptr(cq)
         n, code, mark = self.size, self.program._code, self._mark
         _lib.check(L.col_build_tree_wide(P(self._codes_bufs[1]), P(self._ids_bufs[1]), P(self._nodes_buf),
-                                         P(self._wide_buf), code, n, S), "col_build_tree_wide")
+                                         P(self._wide_buf), P(self._flags_buf), code, n, S), "col_build_tree_wide")
         mark(cq, "tree", 1)
         _lib.check(L.col_refit_wide(P(self._bounds_buf), P(self._wide_buf), P(self._flags_buf), P(self._nodes_buf),
                                     P(coords_buf), P(radii_buf), code, n, S), "col_refit_wide")

@@ -163,10 +163,37 @@ __device__ __forceinline__ Box<T> load_half_cg(const T* wide, size_t node, int h
 }
 
 template <typename T>
+__device__ __forceinline__ void store_both(T* wide, size_t node, const Box<T>& a, const Box<T>& b) {
+    T* p = wide + node * 16;
+    if constexpr (sizeof(T) == 4) {
+        float4* q = reinterpret_cast<float4*>(p);
+        q[0] = make_float4(a.lo[0], a.lo[1], a.lo[2], a.hi[0]);
+        q[1] = make_float4(a.hi[1], a.hi[2], b.lo[0], b.lo[1]);
+        q[2] = make_float4(b.lo[2], b.hi[0], b.hi[1], b.hi[2]);
+    } else {
+        double2* q = reinterpret_cast<double2*>(p);
+        q[0] = make_double2(a.lo[0], a.lo[1]); q[1] = make_double2(a.lo[2], a.hi[0]); q[2] = make_double2(a.hi[1], a.hi[2]);
+        q[3] = make_double2(b.lo[0], b.lo[1]); q[4] = make_double2(b.lo[2], b.hi[0]); q[5] = make_double2(b.hi[1], b.hi[2]);
+    }
+}
+
+// One block = 256 consecutive sorted leaves.  An internal node all of whose leaves lie
+// in that window (marked by the tree kernel in flags[], 255 of every 256 nodes) is
+// resolved entirely inside the block: the first arrival leaves its box in shared memory
+// (block-scope fence + shared-memory counter), the second picks it up, writes the whole
+// traversal record and carries on -- no global atomic, no device-scope fence, no
+// half-written records.  Only nodes spanning several windows take the global path.
+constexpr uint32_t REFIT_IN_BLOCK = 0x80000000u;
+
+template <typename T>
 __global__ void __launch_bounds__(256)
 refit_wide_kernel(T* __restrict__ bounds, T* __restrict__ wide, uint32_t* __restrict__ flags,
                   const col_node* __restrict__ nodes, const T* __restrict__ coords, const T* __restrict__ radii,
                   uint32_t n) {
+    __shared__ T s_box[256][2][6];   // [node & 255][which child][lo xyz, hi xyz]
+    __shared__ unsigned s_cnt[256];
+    s_cnt[threadIdx.x] = 0;
+    __syncthreads();
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const uint32_t leaf_start = n - 1;
@@ -179,11 +206,31 @@ refit_wide_kernel(T* __restrict__ bounds, T* __restrict__ wide, uint32_t* __rest
     while (true) {
         const uint4 rec = __ldg(reinterpret_cast<const uint4*>(nodes + parent));  // {grandparent, right_edge, a, b}
         const int half = rec.z == node ? 0 : 1;
-        store_half(wide, parent, half, box);
-        __threadfence();  // my half is visible before my arrival is
-        if (atomicAdd(flags + parent, 1u) < 1u) return;  // first to arrive: the sibling carries on
-        __threadfence();
-        const Box<T> other = load_half_cg(wide, parent, half ^ 1);
+        Box<T> other;
+        if (__ldg(flags + parent) & REFIT_IN_BLOCK) {
+            const uint32_t slot = parent & 255u;
+#pragma unroll
+            for (int k = 0; k < 3; k++) {
+                s_box[slot][half][k] = box.lo[k];
+                s_box[slot][half][3 + k] = box.hi[k];
+            }
+            __threadfence_block();
+            if (atomicAdd(&s_cnt[slot], 1u) == 0u) return;  // first to arrive: the sibling carries on
+            __threadfence_block();
+#pragma unroll
+            for (int k = 0; k < 3; k++) {
+                other.lo[k] = s_box[slot][half ^ 1][k];
+                other.hi[k] = s_box[slot][half ^ 1][3 + k];
+            }
+            if (half == 0) store_both(wide, parent, box, other);
+            else store_both(wide, parent, other, box);
+        } else {
+            store_half(wide, parent, half, box);
+            __threadfence();  // my half is visible before my arrival is
+            if (atomicAdd(flags + parent, 1u) < 1u) return;
+            __threadfence();
+            other = load_half_cg(wide, parent, half ^ 1);
+        }
 #pragma unroll
         for (int k = 0; k < 3; k++) {
             box.lo[k] = vmin(box.lo[k], other.lo[k]);
@@ -235,7 +282,7 @@ COL_API int col_refit_wide(void* bounds, void* wide, uint32_t* flags, const void
     if (!bounds || !wide || !flags || !nodes || !coords4 || !radii) return COL_ERR_BAD_ARG;
     if (n == 0) return 0;
     cudaStream_t s = col_stream(stream);
-    COL_CUDA(cudaMemsetAsync(flags, 0, sizeof(uint32_t) * (n > 1 ? n - 1 : 1), s));  // only internal nodes count arrivals
+    // flags[] were initialised by col_build_tree_wide (0 or the in-block mark): no memset here
     const unsigned blocks = col_blocks(n, 256);
     if (dtype == COL_F32)
         refit_wide_kernel<float><<<blocks, 256, 0, s>>>((float*)bounds, (float*)wide, flags, (const col_node*)nodes, (const float*)coords4, (const float*)radii, n);

@@ -32,7 +32,8 @@ __device__ __forceinline__ int delta(const uint32_t* __restrict__ codes, uint32_
 template <bool LEAVES, bool WIDE>
 __global__ void __launch_bounds__(256)
 build_tree_kernel(const uint32_t* __restrict__ codes, const uint32_t* __restrict__ ids, col_node* __restrict__ nodes,
-                  uint32_t n, unsigned char* __restrict__ wide, uint32_t wide_stride, uint32_t wide_meta_off) {
+                  uint32_t n, unsigned char* __restrict__ wide, uint32_t wide_stride, uint32_t wide_meta_off,
+                  uint32_t* __restrict__ flags) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const uint32_t leaf_start = n - 1;
@@ -78,8 +79,12 @@ build_tree_kernel(const uint32_t* __restrict__ codes, const uint32_t* __restrict
     rec[3] = child_b;
     nodes[child_a].parent = i;
     nodes[child_b].parent = i;
-    if (WIDE)
+    if (WIDE) {
         *reinterpret_cast<uint4*>(wide + (size_t)i * wide_stride + wide_meta_off) = make_uint4(child_a, child_b, gamma, hi);
+        // arrival word of the refit (refit.cu): marked when all leaves of the node lie in one
+        // 256-leaf window, i.e. inside one refit block, which then resolves it in shared memory
+        flags[i] = ((lo >> 8) == (hi >> 8)) ? 0x80000000u : 0u;
+    }
 }
 
 __global__ void __launch_bounds__(256)
@@ -99,22 +104,22 @@ COL_API int col_build_tree(const uint32_t* codes_sorted, const uint32_t* ids_sor
     if (n > 0x80000000u) return COL_ERR_TOO_LARGE;
     const unsigned blocks = col_blocks(n, 256);
     if (ids_sorted)
-        build_tree_kernel<true, false><<<blocks, 256, 0, col_stream(stream)>>>(codes_sorted, ids_sorted, (col_node*)nodes, n, nullptr, 0, 0);
+        build_tree_kernel<true, false><<<blocks, 256, 0, col_stream(stream)>>>(codes_sorted, ids_sorted, (col_node*)nodes, n, nullptr, 0, 0, nullptr);
     else
-        build_tree_kernel<false, false><<<blocks, 256, 0, col_stream(stream)>>>(codes_sorted, nullptr, (col_node*)nodes, n, nullptr, 0, 0);
+        build_tree_kernel<false, false><<<blocks, 256, 0, col_stream(stream)>>>(codes_sorted, nullptr, (col_node*)nodes, n, nullptr, 0, 0, nullptr);
     COL_CHECK_LAUNCH();
     return 0;
 }
 
 COL_API int col_build_tree_wide(const uint32_t* codes_sorted, const uint32_t* ids_sorted, void* nodes, void* wide,
-                                int dtype, uint32_t n, void* stream) {
-    if (!codes_sorted || !ids_sorted || !nodes || !wide) return COL_ERR_BAD_ARG;
+                                uint32_t* flags, int dtype, uint32_t n, void* stream) {
+    if (!codes_sorted || !ids_sorted || !nodes || !wide || !flags) return COL_ERR_BAD_ARG;
     if (dtype != COL_F32 && dtype != COL_F64) return COL_ERR_UNSUPPORTED;
     if (n == 0) return 0;
     if (n > 0x80000000u) return COL_ERR_TOO_LARGE;
     const uint32_t scalar = dtype == COL_F32 ? 4u : 8u;
     build_tree_kernel<true, true><<<col_blocks(n, 256), 256, 0, col_stream(stream)>>>(
-        codes_sorted, ids_sorted, (col_node*)nodes, n, (unsigned char*)wide, 16 * scalar, 12 * scalar);
+        codes_sorted, ids_sorted, (col_node*)nodes, n, (unsigned char*)wide, 16 * scalar, 12 * scalar, flags);
     COL_CHECK_LAUNCH();
     return 0;
 }

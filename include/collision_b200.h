@@ -164,7 +164,8 @@ int col_traverse_atomic(uint32_t* pairs, uint32_t* counter, uint32_t capacity, c
  *   [0..5] box of child a (lo xyz, hi xyz)   [6..11] box of child b
  *   [12..15] as 4 x u32 in the first 16 bytes: child a, child b,
  *            right_edge(child a), right_edge(child b)
- * `wide`: (n-1) such records.  `bounds` (Bound array) still receives every box;
+ * `wide`: (n-1) such records.  `flags`: n-1 u32 arrival words, initialised by
+ * col_build_tree_wide and consumed by col_refit_wide (call them as a pair).  `bounds` (Bound array) still receives every box;
  * the traversal reads only its leaf part (the query boxes).  The arithmetic and
  * the reported rows are identical to the entry points above.
  *
@@ -176,7 +177,7 @@ int col_traverse_atomic(uint32_t* pairs, uint32_t* counter, uint32_t capacity, c
  * scratch: col_traverse_scratch_bytes(q_end - q_begin).  ids_sorted: ids in sorted order (the sort's
  * payload output). */
 int col_build_tree_wide(const uint32_t* codes_sorted, const uint32_t* ids_sorted, void* nodes, void* wide,
-                        int dtype, uint32_t n, void* stream);
+                        uint32_t* flags, int dtype, uint32_t n, void* stream);
 int col_refit_wide(void* bounds, void* wide, uint32_t* flags, const void* nodes, const void* coords4,
                    const void* radii, int dtype, uint32_t n, void* stream);
 size_t col_traverse_scratch_bytes(uint32_t n_queries);

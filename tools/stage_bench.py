@@ -116,8 +116,9 @@ def main():
     report("traverse atomic (count only)", T(lambda: L.col_traverse_atomic(None, P(n_buf), 0, P(col._nodes_buf), P(col._bounds_buf), code, n, 0, n, S)), 36 * n)
 
     # ---- wide / fused path (the Collider's default)
-    report("build tree + wide meta", T(lambda: L.col_build_tree_wide(P(col._codes_bufs[1]), P(col._ids_bufs[1]), P(col._nodes_buf), P(col._wide_buf), code, n, S)), 56 * n)
-    report("leaf boxes + refit (wide)", T(lambda: L.col_refit_wide(P(col._bounds_buf), P(col._wide_buf), P(col._flags_buf), P(col._nodes_buf), P(coords), P(radii), code, n, S)), 192 * n)
+    report("build tree + wide meta", T(lambda: L.col_build_tree_wide(P(col._codes_bufs[1]), P(col._ids_bufs[1]), P(col._nodes_buf), P(col._wide_buf), P(col._flags_buf), code, n, S)), 60 * n)
+    report("leaf boxes + refit (wide)", T(lambda: L.col_refit_wide(P(col._bounds_buf), P(col._wide_buf), P(col._flags_buf), P(col._nodes_buf), P(coords), P(radii), code, n, S),
+                                          setup=lambda: L.col_build_tree_wide(P(col._codes_bufs[1]), P(col._ids_bufs[1]), P(col._nodes_buf), P(col._wide_buf), P(col._flags_buf), code, n, S)), 192 * n)
     report("traverse wide count", T(lambda: L.col_traverse_wide_count(P(col._total_buf), None, P(col._wide_buf), P(col._bounds_buf), code, n, 0, n, S)), 36 * n)
     report("traverse wide fused (write)", T(lambda: L.col_traverse_wide_pairs(P(pairs), m, 0, P(col._total_buf), P(col._wide_buf), P(col._bounds_buf), P(col._ids_bufs[1]), code, n, 0, n, P(col._trv_scratch), S)), 36 * n + 8 * m)
     torch.cuda.synchronize()
