@@ -157,7 +157,8 @@ class Collider:
         self._counts_buf = _lib.alloc_bytes(ctx, self.size * 4)
         self._scan_scratch = _lib.alloc_bytes(ctx, L.col_scan_scratch_bytes(self.size))
         self._total_buf = torch.zeros(1, dtype=torch.int64, device=ctx)
-        self._wide_buf = _lib.alloc_bytes(ctx, max(self.size - 1, 1) * 16 * self.program.coord_dtype.itemsize)
+        self._wide_buf = _lib.alloc_bytes(ctx, max(self.size - 1, 1) * 32)   # 32-byte traversal records
+        self._scene_buf = _lib.alloc_bytes(ctx, 8 * self.program.coord_dtype.itemsize)   # {min[4], max[4]} of the centres
         self._trv_scratch = _lib.alloc_bytes(ctx, L.col_traverse_scratch_bytes(self.size))
         self._bufs_for = key
 
@@ -205,10 +206,13 @@ class Collider:
         """scene bounds -> Morton codes + ids -> stable sort (collision.py:157-169 upstream)."""
         L, P, S = _lib.lib(), _lib.ptr, _lib.stream_ptr(cq)
         n, code, mark = self.size, self.program._code, self._mark
-        _lib.check(L.col_bounds(P(coords_buf), n, code, 4, P(self._bounds_buf), P(self.reducer._ensure_scratch()), S),
+        # upstream keeps the scene bounds in slot 0 of the Bound array (dual use, collision.py:74-78);
+        # the fast path needs them beyond the refit (grid of the traversal records), so they get a buffer
+        scene = self._scene_buf if self.fast else self._bounds_buf
+        _lib.check(L.col_bounds(P(coords_buf), n, code, 4, P(scene), P(self.reducer._ensure_scratch()), S),
                    "col_bounds")
         mark(cq, "bounds", 1)
-        _lib.check(L.col_morton(P(self._codes_bufs[0]), P(self._ids_bufs[0]), P(coords_buf), P(self._bounds_buf),
+        _lib.check(L.col_morton(P(self._codes_bufs[0]), P(self._ids_bufs[0]), P(coords_buf), P(scene),
                                 code, n, n, S), "col_morton")
         mark(cq, "morton", 1)
         # padding keys are not needed by this sort: only the n real keys move
@@ -222,10 +226,10 @@ class Collider:
         L, P, S = _lib.lib(), _lib.ptr, _lib.stream_ptr(cq)
         n, code, mark = self.size, self.program._code, self._mark
         _lib.check(L.col_build_tree_wide(P(self._codes_bufs[1]), P(self._ids_bufs[1]), P(self._nodes_buf),
-                                         P(self._wide_buf), P(self._flags_buf), code, n, S), "col_build_tree_wide")
+                                         P(self._wide_buf), P(self._flags_buf), n, S), "col_build_tree_wide")
         mark(cq, "tree", 1)
         _lib.check(L.col_refit_wide(P(self._bounds_buf), P(self._wide_buf), P(self._flags_buf), P(self._nodes_buf),
-                                    P(coords_buf), P(radii_buf), code, n, S), "col_refit_wide")
+                                    P(coords_buf), P(radii_buf), P(self._scene_buf), code, n, S), "col_refit_wide")
         mark(cq, "refit", 1)
 
     def _walk_range(self, cq, collisions_buf, n_collisions, q_begin, q_end, base=0):
@@ -234,8 +238,8 @@ class Collider:
         order.  Leaves the u64 row count of the range in self._total_buf."""
         L, P, S = _lib.lib(), _lib.ptr, _lib.stream_ptr(cq)
         _lib.check(L.col_traverse_wide_pairs(P(collisions_buf), n_collisions, base, P(self._total_buf),
-                                             P(self._wide_buf), P(self._bounds_buf), P(self._ids_bufs[1]),
-                                             self.program._code, self.size, q_begin, q_end,
+                                             P(self._wide_buf), P(self._bounds_buf), P(self._scene_buf),
+                                             P(self._ids_bufs[1]), self.program._code, self.size, q_begin, q_end,
                                              P(self._trv_scratch), S), "col_traverse_wide_pairs")
         self._mark(cq, "traverse_pairs" if n_collisions else "traverse_count", 3 if n_collisions else 1)
 

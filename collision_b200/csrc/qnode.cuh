@@ -1,0 +1,62 @@
+// qnode.cuh -- the 32-byte traversal record and its conservative quantisation.
+//
+// One record per internal node (written by tree.cu + refit.cu, read by traverse_wide.cu):
+//   w0 = child a, w1 = child b,
+//   w2..w4 = box of child a, w5..w7 = box of child b, each as 6 x u16 {lo.x lo.y lo.z hi.x hi.y hi.z}
+// A visit is ONE 256-bit load.  The u16 coordinates live on a 65536^3 grid spanning the scene
+// bounds (of the centres; anything outside clamps to the border cells) and are rounded
+// OUTWARD (floor for lo, ceil for hi), the query box likewise, and compared with >= / <=:
+// an exact overlap always implies a grid overlap, so an internal node is never pruned
+// wrongly; at worst a few extra nodes are visited.  The decision that matters -- is a LEAF
+// reported -- is always taken on the exact float boxes, exactly as collision.cl:164-166
+// does; since every ancestor's exact box contains the leaf's, the reported set and its DFS
+// order are identical to the reference walk's.
+//
+// Right edges need no storage: child a of node X is a left child, so in Karras numbering
+// its index IS its right edge (internal) or index - (n-1) (leaf); child b's right edge is
+// X's own, which was already checked (> q) when X was entered.
+#pragma once
+#include "common.cuh"
+
+template <typename T> struct Quant {
+    T lo[3], scale[3];
+};
+
+template <typename T>
+__device__ __forceinline__ Quant<T> make_quant(const T* __restrict__ scene /* {min[4], max[4]} */) {
+    Quant<T> qz;
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+        const T lo = scene[k], ext = scene[4 + k] - scene[k];
+        qz.lo[k] = lo;
+        qz.scale[k] = ext > (T)0 ? (T)65535 / ext : (T)0;  // degenerate / NaN extent: everything maps to cell 0
+    }
+    return qz;
+}
+
+// monotone non-decreasing in x (subtract and multiply by a non-negative constant, each
+// correctly rounded, then clamp); NaN -> 0
+__device__ __forceinline__ float grid_coord(float x, float lo, float scale) {
+    return fminf(fmaxf(__fmul_rn(__fsub_rn(x, lo), scale), 0.0f), 65535.0f);
+}
+__device__ __forceinline__ double grid_coord(double x, double lo, double scale) {
+    return fmin(fmax(__dmul_rn(__dsub_rn(x, lo), scale), 0.0), 65535.0);
+}
+__device__ __forceinline__ uint32_t grid_floor(float t) { return (uint32_t)__float2int_rd(t); }
+__device__ __forceinline__ uint32_t grid_ceil(float t) { return (uint32_t)__float2int_ru(t); }
+__device__ __forceinline__ uint32_t grid_floor(double t) { return (uint32_t)__double2int_rd(t); }
+__device__ __forceinline__ uint32_t grid_ceil(double t) { return (uint32_t)__double2int_ru(t); }
+
+// box {lo[3], hi[3]} -> 3 words of 6 x u16, rounded outward
+template <typename T>
+__device__ __forceinline__ uint3 quantise_box(const Quant<T>& qz, const T (&lo)[3], const T (&hi)[3]) {
+    uint32_t v[6];
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+        v[k] = grid_floor(grid_coord(lo[k], qz.lo[k], qz.scale[k]));
+        v[3 + k] = grid_ceil(grid_coord(hi[k], qz.lo[k], qz.scale[k]));
+    }
+    return make_uint3(v[0] | (v[1] << 16), v[2] | (v[3] << 16), v[4] | (v[5] << 16));
+}
+
+constexpr uint32_t QNODE_BYTES = 32;

@@ -10,6 +10,7 @@
 // and only reads the sibling's from memory (L2-coherent ld.global.cg after a
 // __threadfence on both sides), halving the box re-reads of the reference.
 #include "common.cuh"
+#include "qnode.cuh"
 
 namespace {
 
@@ -108,94 +109,28 @@ refit_kernel(T* __restrict__ bounds, uint32_t* __restrict__ flags, const col_nod
     }
 }
 
-// ---- traversal ("wide") nodes -------------------------------------------
-// One record of 16 scalars per internal node, laid out for the traversal:
-//   [0..5]  box of child a (lo xyz, hi xyz)     [6..11] box of child b
-//   [12..15] (as u32 x4, in the first 16 bytes) child a, child b, right_edge a, right_edge b
-// 64 bytes for f32 / 128 for f64: everything a visit needs comes from one
-// contiguous record instead of five cache lines of the Node/Bound arrays.  The
-// index part is written by the tree kernel; here each arriving thread stores
-// its own child's box into its half BEFORE announcing its arrival, and the
-// second arrival reads the other half (so no Bound array is needed for the
-// walk itself).  The Node/Bound arrays are still filled (reference layout).
-template <typename T>
-__device__ __forceinline__ void store_half(T* wide, size_t node, int half, const Box<T>& b) {
-    T* p = wide + node * 16 + half * 6;
-    if constexpr (sizeof(T) == 4) {
-        if (half == 0) {
-            *reinterpret_cast<float4*>(p) = make_float4(b.lo[0], b.lo[1], b.lo[2], b.hi[0]);
-            *reinterpret_cast<float2*>(p + 4) = make_float2(b.hi[1], b.hi[2]);
-        } else {
-            *reinterpret_cast<float2*>(p) = make_float2(b.lo[0], b.lo[1]);
-            *reinterpret_cast<float4*>(p + 2) = make_float4(b.lo[2], b.hi[0], b.hi[1], b.hi[2]);
-        }
-    } else {
-        double2* q = reinterpret_cast<double2*>(p);
-        q[0] = make_double2(b.lo[0], b.lo[1]);
-        q[1] = make_double2(b.lo[2], b.hi[0]);
-        q[2] = make_double2(b.hi[1], b.hi[2]);
-    }
-}
-template <typename T>
-__device__ __forceinline__ Box<T> load_half_cg(const T* wide, size_t node, int half) {
-    const T* p = wide + node * 16 + half * 6;
-    Box<T> b;
-    if constexpr (sizeof(T) == 4) {
-        float v[6];
-        if (half == 0) {
-            const float4 a = ld_cg_f4(reinterpret_cast<const float4*>(p));
-            float2 c;
-            asm volatile("ld.global.cg.v2.f32 {%0,%1}, [%2];" : "=f"(c.x), "=f"(c.y) : "l"(p + 4) : "memory");
-            v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = c.x; v[5] = c.y;
-        } else {
-            float2 c;
-            asm volatile("ld.global.cg.v2.f32 {%0,%1}, [%2];" : "=f"(c.x), "=f"(c.y) : "l"(p) : "memory");
-            const float4 a = ld_cg_f4(reinterpret_cast<const float4*>(p + 2));
-            v[0] = c.x; v[1] = c.y; v[2] = a.x; v[3] = a.y; v[4] = a.z; v[5] = a.w;
-        }
-        b.lo[0] = v[0]; b.lo[1] = v[1]; b.lo[2] = v[2]; b.hi[0] = v[3]; b.hi[1] = v[4]; b.hi[2] = v[5];
-    } else {
-        const double2* q = reinterpret_cast<const double2*>(p);
-        const double2 a = ld_cg_d2(q), c = ld_cg_d2(q + 1), d = ld_cg_d2(q + 2);
-        b.lo[0] = a.x; b.lo[1] = a.y; b.lo[2] = c.x; b.hi[0] = c.y; b.hi[1] = d.x; b.hi[2] = d.y;
-    }
-    return b;
-}
-
-template <typename T>
-__device__ __forceinline__ void store_both(T* wide, size_t node, const Box<T>& a, const Box<T>& b) {
-    T* p = wide + node * 16;
-    if constexpr (sizeof(T) == 4) {
-        float4* q = reinterpret_cast<float4*>(p);
-        q[0] = make_float4(a.lo[0], a.lo[1], a.lo[2], a.hi[0]);
-        q[1] = make_float4(a.hi[1], a.hi[2], b.lo[0], b.lo[1]);
-        q[2] = make_float4(b.lo[2], b.hi[0], b.hi[1], b.hi[2]);
-    } else {
-        double2* q = reinterpret_cast<double2*>(p);
-        q[0] = make_double2(a.lo[0], a.lo[1]); q[1] = make_double2(a.lo[2], a.hi[0]); q[2] = make_double2(a.hi[1], a.hi[2]);
-        q[3] = make_double2(b.lo[0], b.lo[1]); q[4] = make_double2(b.lo[2], b.hi[0]); q[5] = make_double2(b.hi[1], b.hi[2]);
-    }
-}
-
+// ---- refit emitting the traversal records (qnode.cuh) -------------------------
 // One block = 256 consecutive sorted leaves.  An internal node all of whose leaves lie
 // in that window (marked by the tree kernel in flags[], 255 of every 256 nodes) is
-// resolved entirely inside the block: the first arrival leaves its box in shared memory
-// (block-scope fence + shared-memory counter), the second picks it up, writes the whole
-// traversal record and carries on -- no global atomic, no device-scope fence, no
-// half-written records.  Only nodes spanning several windows take the global path.
+// resolved entirely inside the block: both arrivals leave their exact box in shared
+// memory (block-scope fence + shared-memory counter), the second merges, quantises BOTH
+// child boxes and writes the node's traversal record in one go -- no global atomic, no
+// device-scope fence.  Only nodes spanning several windows take the global path, where
+// the sibling's exact box is read back from the Bound array.
 constexpr uint32_t REFIT_IN_BLOCK = 0x80000000u;
 
 template <typename T>
 __global__ void __launch_bounds__(256)
-refit_wide_kernel(T* __restrict__ bounds, T* __restrict__ wide, uint32_t* __restrict__ flags,
+refit_wide_kernel(T* __restrict__ bounds, unsigned char* __restrict__ wide, uint32_t* __restrict__ flags,
                   const col_node* __restrict__ nodes, const T* __restrict__ coords, const T* __restrict__ radii,
-                  uint32_t n) {
+                  const T* __restrict__ scene, uint32_t n) {
     __shared__ T s_box[256][2][6];   // [node & 255][which child][lo xyz, hi xyz]
     __shared__ unsigned s_cnt[256];
     s_cnt[threadIdx.x] = 0;
     __syncthreads();
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
+    const Quant<T> qz = make_quant(scene);
     const uint32_t leaf_start = n - 1;
     uint32_t node = leaf_start + i;
     const uint4 leaf = __ldg(reinterpret_cast<const uint4*>(nodes + node));  // {parent, right_edge, id, -}
@@ -222,14 +157,19 @@ refit_wide_kernel(T* __restrict__ bounds, T* __restrict__ wide, uint32_t* __rest
                 other.lo[k] = s_box[slot][half ^ 1][k];
                 other.hi[k] = s_box[slot][half ^ 1][3 + k];
             }
-            if (half == 0) store_both(wide, parent, box, other);
-            else store_both(wide, parent, other, box);
         } else {
-            store_half(wide, parent, half, box);
-            __threadfence();  // my half is visible before my arrival is
+            // my exact box is already in the Bound array (stored below / at the leaf)
+            __threadfence();  // ... and visible before my arrival is
             if (atomicAdd(flags + parent, 1u) < 1u) return;
             __threadfence();
-            other = load_half_cg(wide, parent, half ^ 1);
+            other = load_box_cg(bounds, half == 0 ? rec.w : rec.z);
+        }
+        {   // the node's traversal record: both children, quantised outward
+            const uint3 mine = quantise_box(qz, box.lo, box.hi), sib = quantise_box(qz, other.lo, other.hi);
+            const uint3 qa = half == 0 ? mine : sib, qb = half == 0 ? sib : mine;
+            unsigned char* rp = wide + (size_t)parent * QNODE_BYTES;
+            *reinterpret_cast<uint2*>(rp + 8) = make_uint2(qa.x, qa.y);
+            *reinterpret_cast<uint4*>(rp + 16) = make_uint4(qa.z, qb.x, qb.y, qb.z);
         }
 #pragma unroll
         for (int k = 0; k < 3; k++) {
@@ -278,16 +218,17 @@ COL_API int col_refit(void* bounds, uint32_t* flags, const void* nodes, const vo
 }
 
 COL_API int col_refit_wide(void* bounds, void* wide, uint32_t* flags, const void* nodes, const void* coords4,
-                           const void* radii, int dtype, uint32_t n, void* stream) {
-    if (!bounds || !wide || !flags || !nodes || !coords4 || !radii) return COL_ERR_BAD_ARG;
+                           const void* radii, const void* scene2x4, int dtype, uint32_t n, void* stream) {
+    if (!bounds || !wide || !flags || !nodes || !coords4 || !radii || !scene2x4) return COL_ERR_BAD_ARG;
+    if (scene2x4 == bounds) return COL_ERR_BAD_ARG;  // slot 0 of the Bound array is overwritten with the root box
     if (n == 0) return 0;
     cudaStream_t s = col_stream(stream);
     // flags[] were initialised by col_build_tree_wide (0 or the in-block mark): no memset here
     const unsigned blocks = col_blocks(n, 256);
     if (dtype == COL_F32)
-        refit_wide_kernel<float><<<blocks, 256, 0, s>>>((float*)bounds, (float*)wide, flags, (const col_node*)nodes, (const float*)coords4, (const float*)radii, n);
+        refit_wide_kernel<float><<<blocks, 256, 0, s>>>((float*)bounds, (unsigned char*)wide, flags, (const col_node*)nodes, (const float*)coords4, (const float*)radii, (const float*)scene2x4, n);
     else if (dtype == COL_F64)
-        refit_wide_kernel<double><<<blocks, 256, 0, s>>>((double*)bounds, (double*)wide, flags, (const col_node*)nodes, (const double*)coords4, (const double*)radii, n);
+        refit_wide_kernel<double><<<blocks, 256, 0, s>>>((double*)bounds, (unsigned char*)wide, flags, (const col_node*)nodes, (const double*)coords4, (const double*)radii, (const double*)scene2x4, n);
     else
         return COL_ERR_UNSUPPORTED;
     COL_CHECK_LAUNCH();

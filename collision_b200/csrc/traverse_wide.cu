@@ -4,10 +4,11 @@
 // Same walk as collision/collision.cl:174-226 (see traverse.cu, which keeps the
 // reference's Node/Bound argument contract), restructured around HBM/L1 traffic:
 //
-//  * one 64-byte (f32) / 128-byte (f64) record per internal node holds both
-//    children's boxes, indices and right edges (written by tree.cu + refit.cu):
-//    a visit is two 256-bit loads from one line instead of seven 128-bit loads
-//    from five lines (the profile of the Node/Bound walk is L1-sector bound).
+//  * one 32-byte record per internal node (qnode.cuh) holds both children's indices and
+//    their boxes on a conservative u16 grid: a visit is ONE 256-bit load instead of seven
+//    128-bit loads from five lines (ncu: the walk is bound by L1 data-pipe wavefronts, one
+//    per diverged lane per load).  Leaves are confirmed on the exact float boxes, so the
+//    reported rows and their order are the reference's, bit for bit.
 //  * count -> scan -> write without a second walk: every query walks once and
 //    parks its first TRV_STASH hits in a k-major global array (coalesced rows, only
 //    the used ones move); the counts are scanned by the single-pass scan kernel;
@@ -18,82 +19,104 @@
 //    decoupled look-back was measured slower: blocks of dense regions stall every
 //    later block, and a shared-memory stash shrinks the L1 the walk depends on.)
 #include "common.cuh"
+#include "qnode.cuh"
 
 namespace {
 
 constexpr int TRV_THREADS = 128;
 constexpr int TRV_STASH = 32;
 
-template <typename T> struct WNode {
-    T a[6], b[6];
-    uint32_t ca, cb, ra, rb;
+struct QNode {
+    uint32_t ca, cb;
+    uint32_t a[6], b[6];  // lo xyz, hi xyz on the u16 grid
 };
 
-__device__ __forceinline__ void load_wide(const float* __restrict__ wide, uint32_t idx, WNode<float>& w) {
-    const float* p = wide + (size_t)idx * 16;
-    float v[8];
-    uint32_t u[4];
-    asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
-                 : "=f"(w.a[0]), "=f"(w.a[1]), "=f"(w.a[2]), "=f"(w.a[3]), "=f"(w.a[4]), "=f"(w.a[5]), "=f"(w.b[0]),
-                   "=f"(w.b[1])
-                 : "l"(p));
+__device__ __forceinline__ QNode load_qnode(const unsigned char* __restrict__ wide, uint32_t idx) {
+    uint32_t w[8];
     asm volatile("ld.global.nc.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
-                 : "=f"(v[0]), "=f"(v[1]), "=f"(v[2]), "=f"(v[3]), "=r"(u[0]), "=r"(u[1]), "=r"(u[2]), "=r"(u[3])
-                 : "l"(p + 8));
-    w.b[2] = v[0]; w.b[3] = v[1]; w.b[4] = v[2]; w.b[5] = v[3];
-    w.ca = u[0]; w.cb = u[1]; w.ra = u[2]; w.rb = u[3];
-}
-__device__ __forceinline__ void load_wide(const double* __restrict__ wide, uint32_t idx, WNode<double>& w) {
-    const double* p = wide + (size_t)idx * 16;
-    double v[12];
-#pragma unroll
-    for (int k = 0; k < 3; k++)
-        asm volatile("ld.global.nc.v4.f64 {%0,%1,%2,%3}, [%4];"
-                     : "=d"(v[4 * k]), "=d"(v[4 * k + 1]), "=d"(v[4 * k + 2]), "=d"(v[4 * k + 3])
-                     : "l"(p + 4 * k));
-    const uint4 m = __ldg(reinterpret_cast<const uint4*>(p + 12));
-#pragma unroll
-    for (int k = 0; k < 6; k++) { w.a[k] = v[k]; w.b[k] = v[6 + k]; }
-    w.ca = m.x; w.cb = m.y; w.ra = m.z; w.rb = m.w;
+                 : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]), "=r"(w[4]), "=r"(w[5]), "=r"(w[6]), "=r"(w[7])
+                 : "l"(wide + (size_t)idx * QNODE_BYTES));
+    QNode q;
+    q.ca = w[0]; q.cb = w[1];
+    q.a[0] = w[2] & 0xFFFFu; q.a[1] = w[2] >> 16; q.a[2] = w[3] & 0xFFFFu;
+    q.a[3] = w[3] >> 16;     q.a[4] = w[4] & 0xFFFFu; q.a[5] = w[4] >> 16;
+    q.b[0] = w[5] & 0xFFFFu; q.b[1] = w[5] >> 16; q.b[2] = w[6] & 0xFFFFu;
+    q.b[3] = w[6] >> 16;     q.b[4] = w[7] & 0xFFFFu; q.b[5] = w[7] >> 16;
+    return q;
 }
 
-template <typename T> struct Query { T lo[3], hi[3]; };
+// exact query box + its outward-rounded grid image
+template <typename T> struct Query {
+    T lo[3], hi[3];
+    uint32_t glo[3], ghi[3];
+};
 
-__device__ __forceinline__ Query<float> load_query(const float* __restrict__ bounds, uint32_t node) {
-    const float4* p = reinterpret_cast<const float4*>(bounds) + (size_t)node * 2;
-    const float4 a = __ldg(p), c = __ldg(p + 1);
-    return {{a.x, a.y, a.z}, {c.x, c.y, c.z}};
+template <typename T> struct LeafBox { T lo[3], hi[3]; };
+
+__device__ __forceinline__ LeafBox<float> load_leaf_box(const float* __restrict__ bounds, uint32_t node) {
+    float v[8];
+    asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=f"(v[0]), "=f"(v[1]), "=f"(v[2]), "=f"(v[3]), "=f"(v[4]), "=f"(v[5]), "=f"(v[6]), "=f"(v[7])
+                 : "l"(bounds + (size_t)node * 8));
+    return {{v[0], v[1], v[2]}, {v[4], v[5], v[6]}};
 }
-__device__ __forceinline__ Query<double> load_query(const double* __restrict__ bounds, uint32_t node) {
+__device__ __forceinline__ LeafBox<double> load_leaf_box(const double* __restrict__ bounds, uint32_t node) {
     const double2* p = reinterpret_cast<const double2*>(bounds) + (size_t)node * 4;
     const double2 a = __ldg(p), c = __ldg(p + 1), d = __ldg(p + 2), e = __ldg(p + 3);
     return {{a.x, a.y, c.x}, {d.x, d.y, e.x}};
 }
 
-// collision.cl:164-166: all(q.max > c.min & q.min < c.max), strict, x y z
 template <typename T>
-__device__ __forceinline__ bool overlap(const Query<T>& q, const T (&c)[6]) {
-    return (q.hi[0] > c[0]) & (q.lo[0] < c[3]) & (q.hi[1] > c[1]) & (q.lo[1] < c[4]) & (q.hi[2] > c[2]) &
-           (q.lo[2] < c[5]);
+__device__ __forceinline__ Query<T> load_query(const T* __restrict__ bounds, uint32_t node, const Quant<T>& qz) {
+    const LeafBox<T> b = load_leaf_box(bounds, node);
+    Query<T> q;
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+        q.lo[k] = b.lo[k];
+        q.hi[k] = b.hi[k];
+        q.glo[k] = grid_floor(grid_coord(b.lo[k], qz.lo[k], qz.scale[k]));
+        q.ghi[k] = grid_ceil(grid_coord(b.hi[k], qz.lo[k], qz.scale[k]));
+    }
+    return q;
 }
 
-// One DFS walk.  on_hit(leaf_position) is called for every reported leaf in
-// reference order.  Returns the number of hits.
+// conservative test on the grid (see qnode.cuh): never false when the exact boxes overlap
+template <typename T>
+__device__ __forceinline__ bool grid_overlap(const Query<T>& q, const uint32_t (&c)[6]) {
+    return (q.ghi[0] >= c[0]) & (q.glo[0] <= c[3]) & (q.ghi[1] >= c[1]) & (q.glo[1] <= c[4]) & (q.ghi[2] >= c[2]) &
+           (q.glo[2] <= c[5]);
+}
+// collision.cl:164-166: all(q.max > c.min & q.min < c.max), strict, x y z -- on the exact boxes
+template <typename T>
+__device__ __forceinline__ bool exact_overlap(const Query<T>& q, const LeafBox<T>& c) {
+    return (q.hi[0] > c.lo[0]) & (q.lo[0] < c.hi[0]) & (q.hi[1] > c.lo[1]) & (q.lo[1] < c.hi[1]) &
+           (q.hi[2] > c.lo[2]) & (q.lo[2] < c.hi[2]);
+}
+
+// One DFS walk (collision.cl:174-226).  on_hit(leaf_position, k) is called for the k-th
+// reported leaf, in reference order.  Returns the number of hits.
 template <typename T, typename F>
-__device__ __forceinline__ uint32_t walk(const T* __restrict__ wide, const Query<T>& query, uint32_t q,
-                                         uint32_t leaf_start, F&& on_hit) {
+__device__ __forceinline__ uint32_t walk(const unsigned char* __restrict__ wide, const T* __restrict__ bounds,
+                                         const Query<T>& query, uint32_t q, uint32_t leaf_start, F&& on_hit) {
+    if (q >= leaf_start) return 0;  // the last sorted leaf has nothing to its right (every right_edge <= q)
     uint32_t stack[64];
     int sp = 0;
     stack[sp++] = 0xFFFFFFFFu;
     uint32_t idx = 0, hits = 0;
     do {
-        WNode<T> w;
-        load_wide(wide, idx, w);
-        const bool oa = overlap(query, w.a) && !(w.ra <= q);
-        const bool ob = overlap(query, w.b) && !(w.rb <= q);
+        const QNode w = load_qnode(wide, idx);
         const bool la = w.ca >= leaf_start, lb = w.cb >= leaf_start;
-        if (oa && la) { on_hit(w.ca - leaf_start, hits); hits++; }
-        if (ob && lb) { on_hit(w.cb - leaf_start, hits); hits++; }
+        // child a is a left child: its right edge is its own index (leaf: its position);
+        // child b's right edge is this node's, already known to be > q
+        const uint32_t ra = la ? w.ca - leaf_start : w.ca;
+        bool oa = grid_overlap(query, w.a) && ra > q;
+        bool ob = grid_overlap(query, w.b);
+        if (oa && la) {
+            if (exact_overlap(query, load_leaf_box(bounds, w.ca))) { on_hit(w.ca - leaf_start, hits); hits++; }
+        }
+        if (ob && lb) {
+            if (exact_overlap(query, load_leaf_box(bounds, w.cb))) { on_hit(w.cb - leaf_start, hits); hits++; }
+        }
         const bool ta = oa && !la, tb = ob && !lb;
         if (!ta && !tb) {
             idx = stack[--sp];
@@ -108,14 +131,14 @@ __device__ __forceinline__ uint32_t walk(const T* __restrict__ wide, const Query
 // ---- count only: per-block sum -> one atomic per block ----------------------
 template <typename T>
 __global__ void __launch_bounds__(TRV_THREADS)
-count_kernel(unsigned long long* __restrict__ total, uint32_t* __restrict__ counts, const T* __restrict__ wide,
-             const T* __restrict__ bounds, uint32_t n, uint32_t q_begin, uint32_t q_end) {
+count_kernel(unsigned long long* __restrict__ total, uint32_t* __restrict__ counts, const unsigned char* __restrict__ wide,
+             const T* __restrict__ bounds, const T* __restrict__ scene, uint32_t n, uint32_t q_begin, uint32_t q_end) {
     const uint32_t q = q_begin + blockIdx.x * TRV_THREADS + threadIdx.x;
     const uint32_t leaf_start = n - 1;
     uint32_t hits = 0;
     if (q < q_end) {
-        const Query<T> query = load_query(bounds, leaf_start + q);
-        hits = walk(wide, query, q, leaf_start, [](uint32_t, uint32_t) {});
+        const Query<T> query = load_query(bounds, leaf_start + q, make_quant(scene));
+        hits = walk(wide, bounds, query, q, leaf_start, [](uint32_t, uint32_t) {});
         if (counts) counts[q - q_begin] = hits;
     }
     __shared__ uint32_t s_sum[TRV_THREADS / 32];
@@ -140,17 +163,17 @@ count_kernel(unsigned long long* __restrict__ total, uint32_t* __restrict__ coun
 template <typename T>
 __global__ void __launch_bounds__(TRV_THREADS)
 walk_park_kernel(unsigned long long* __restrict__ total, uint32_t* __restrict__ counts, uint32_t* __restrict__ stash,
-                 const T* __restrict__ wide, const T* __restrict__ bounds, uint32_t n, uint32_t q_begin,
-                 uint32_t q_end) {
+                 const unsigned char* __restrict__ wide, const T* __restrict__ bounds, const T* __restrict__ scene,
+                 uint32_t n, uint32_t q_begin, uint32_t q_end) {
     const uint32_t i = blockIdx.x * TRV_THREADS + threadIdx.x;
     const uint32_t q = q_begin + i;
     const uint32_t nq = q_end - q_begin;
     const uint32_t leaf_start = n - 1;
     uint32_t hits = 0;
     if (q < q_end) {
-        const Query<T> query = load_query(bounds, leaf_start + q);
+        const Query<T> query = load_query(bounds, leaf_start + q, make_quant(scene));
         uint32_t* park = stash + i;
-        hits = walk(wide, query, q, leaf_start, [park, nq](uint32_t pos, uint32_t k) {
+        hits = walk(wide, bounds, query, q, leaf_start, [park, nq](uint32_t pos, uint32_t k) {
             if (k < TRV_STASH) park[(size_t)k * nq] = pos;
         });
         counts[i] = hits;
@@ -177,8 +200,8 @@ template <typename T>
 __global__ void __launch_bounds__(TRV_THREADS)
 emit_kernel(uint32_t* __restrict__ pairs, uint64_t capacity, uint64_t base, const uint32_t* __restrict__ offsets,
             const unsigned long long* __restrict__ total, const uint32_t* __restrict__ stash,
-            const T* __restrict__ wide, const T* __restrict__ bounds, const uint32_t* __restrict__ ids, uint32_t n,
-            uint32_t q_begin, uint32_t q_end) {
+            const unsigned char* __restrict__ wide, const T* __restrict__ bounds, const T* __restrict__ scene,
+            const uint32_t* __restrict__ ids, uint32_t n, uint32_t q_begin, uint32_t q_end) {
     const uint32_t i = blockIdx.x * TRV_THREADS + threadIdx.x;
     const uint32_t q = q_begin + i;
     if (q >= q_end) return;
@@ -197,8 +220,8 @@ emit_kernel(uint32_t* __restrict__ pairs, uint64_t capacity, uint64_t base, cons
     }
     if (hits > TRV_STASH) {
         const uint32_t leaf_start = n - 1;
-        const Query<T> query = load_query(bounds, leaf_start + q);
-        walk(wide, query, q, leaf_start, [=](uint32_t pos, uint32_t k) {
+        const Query<T> query = load_query(bounds, leaf_start + q, make_quant(scene));
+        walk(wide, bounds, query, q, leaf_start, [=](uint32_t pos, uint32_t k) {
             const uint64_t at = out + k;
             if (k >= TRV_STASH && at < capacity)
                 *reinterpret_cast<uint2*>(pairs + at * 2) = make_uint2(qid, __ldg(ids + pos));
@@ -210,16 +233,16 @@ emit_kernel(uint32_t* __restrict__ pairs, uint64_t capacity, uint64_t base, cons
 template <typename T>
 __global__ void __launch_bounds__(TRV_THREADS)
 write_kernel(uint32_t* __restrict__ pairs, uint64_t capacity, const uint32_t* __restrict__ offsets, uint64_t base,
-             const T* __restrict__ wide, const T* __restrict__ bounds, const uint32_t* __restrict__ ids, uint32_t n,
-             uint32_t q_begin, uint32_t q_end) {
+             const unsigned char* __restrict__ wide, const T* __restrict__ bounds, const T* __restrict__ scene,
+             const uint32_t* __restrict__ ids, uint32_t n, uint32_t q_begin, uint32_t q_end) {
     const uint32_t q = q_begin + blockIdx.x * TRV_THREADS + threadIdx.x;
     if (q >= q_end) return;
     const uint32_t leaf_start = n - 1;
     const uint64_t out = base + offsets[q - q_begin];
     if (out >= capacity) return;
-    const Query<T> query = load_query(bounds, leaf_start + q);
+    const Query<T> query = load_query(bounds, leaf_start + q, make_quant(scene));
     const uint32_t qid = __ldg(ids + q);
-    walk(wide, query, q, leaf_start, [=](uint32_t pos, uint32_t k) {
+    walk(wide, bounds, query, q, leaf_start, [=](uint32_t pos, uint32_t k) {
         const uint64_t at = out + k;
         if (at < capacity) *reinterpret_cast<uint2*>(pairs + at * 2) = make_uint2(qid, __ldg(ids + pos));
     });
@@ -243,31 +266,35 @@ static PairsLayout pairs_layout(uint32_t nq) {
 
 COL_API size_t col_traverse_scratch_bytes(uint32_t n_queries) { return pairs_layout(n_queries ? n_queries : 1).total; }
 
-COL_API int col_traverse_wide_count(uint64_t* total, uint32_t* counts, const void* wide, const void* bounds, int dtype,
-                                    uint32_t n, uint32_t q_begin, uint32_t q_end, void* stream) {
-    if (!wide || !bounds || bad_range(n, q_begin, q_end)) return COL_ERR_BAD_ARG;
+COL_API int col_traverse_wide_count(uint64_t* total, uint32_t* counts, const void* wide, const void* bounds,
+                                    const void* scene2x4, int dtype, uint32_t n, uint32_t q_begin, uint32_t q_end,
+                                    void* stream) {
+    if (!wide || !bounds || !scene2x4 || bad_range(n, q_begin, q_end)) return COL_ERR_BAD_ARG;
+    if (dtype != COL_F32 && dtype != COL_F64) return COL_ERR_UNSUPPORTED;
     cudaStream_t s = col_stream(stream);
     if (total) COL_CUDA(cudaMemsetAsync(total, 0, sizeof(uint64_t), s));
     if (q_begin == q_end) return 0;
     if (n < 2) return counts ? (int)cudaMemsetAsync(counts, 0, sizeof(uint32_t) * (q_end - q_begin), s) : 0;
     const unsigned blocks = col_blocks(q_end - q_begin, TRV_THREADS);
+    const unsigned char* w = (const unsigned char*)wide;
     if (dtype == COL_F32)
-        count_kernel<float><<<blocks, TRV_THREADS, 0, s>>>((unsigned long long*)total, counts, (const float*)wide, (const float*)bounds, n, q_begin, q_end);
-    else if (dtype == COL_F64)
-        count_kernel<double><<<blocks, TRV_THREADS, 0, s>>>((unsigned long long*)total, counts, (const double*)wide, (const double*)bounds, n, q_begin, q_end);
+        count_kernel<float><<<blocks, TRV_THREADS, 0, s>>>((unsigned long long*)total, counts, w, (const float*)bounds, (const float*)scene2x4, n, q_begin, q_end);
     else
-        return COL_ERR_UNSUPPORTED;
+        count_kernel<double><<<blocks, TRV_THREADS, 0, s>>>((unsigned long long*)total, counts, w, (const double*)bounds, (const double*)scene2x4, n, q_begin, q_end);
     COL_CHECK_LAUNCH();
     return 0;
 }
 
 COL_API int col_traverse_wide_pairs(uint32_t* pairs, uint64_t capacity, uint64_t base, uint64_t* total_out,
-                                    const void* wide, const void* bounds, const uint32_t* ids_sorted, int dtype,
-                                    uint32_t n, uint32_t q_begin, uint32_t q_end, void* scratch, void* stream) {
-    if (!wide || !bounds || !ids_sorted || !scratch || !total_out || bad_range(n, q_begin, q_end) || (!pairs && capacity))
+                                    const void* wide, const void* bounds, const void* scene2x4,
+                                    const uint32_t* ids_sorted, int dtype, uint32_t n, uint32_t q_begin,
+                                    uint32_t q_end, void* scratch, void* stream) {
+    if (!wide || !bounds || !scene2x4 || !ids_sorted || !scratch || !total_out || bad_range(n, q_begin, q_end) ||
+        (!pairs && capacity))
         return COL_ERR_BAD_ARG;
     if (dtype != COL_F32 && dtype != COL_F64) return COL_ERR_UNSUPPORTED;
-    if (capacity == 0) return col_traverse_wide_count(total_out, nullptr, wide, bounds, dtype, n, q_begin, q_end, stream);
+    if (capacity == 0)
+        return col_traverse_wide_count(total_out, nullptr, wide, bounds, scene2x4, dtype, n, q_begin, q_end, stream);
     cudaStream_t s = col_stream(stream);
     COL_CUDA(cudaMemsetAsync(total_out, 0, sizeof(uint64_t), s));
     if (q_begin == q_end || n < 2) return 0;
@@ -278,35 +305,37 @@ COL_API int col_traverse_wide_pairs(uint32_t* pairs, uint64_t capacity, uint64_t
     uint32_t* stash = reinterpret_cast<uint32_t*>(sc + L.stash);
     unsigned long long* total = reinterpret_cast<unsigned long long*>(total_out);
     const unsigned blocks = col_blocks(nq, TRV_THREADS);
+    const unsigned char* w = (const unsigned char*)wide;
     if (dtype == COL_F32)
-        walk_park_kernel<float><<<blocks, TRV_THREADS, 0, s>>>(total, counts, stash, (const float*)wide, (const float*)bounds, n, q_begin, q_end);
+        walk_park_kernel<float><<<blocks, TRV_THREADS, 0, s>>>(total, counts, stash, w, (const float*)bounds, (const float*)scene2x4, n, q_begin, q_end);
     else
-        walk_park_kernel<double><<<blocks, TRV_THREADS, 0, s>>>(total, counts, stash, (const double*)wide, (const double*)bounds, n, q_begin, q_end);
+        walk_park_kernel<double><<<blocks, TRV_THREADS, 0, s>>>(total, counts, stash, w, (const double*)bounds, (const double*)scene2x4, n, q_begin, q_end);
     COL_CHECK_LAUNCH();
     const int rc = col_exclusive_scan_u32(counts, nq, nullptr, sc + L.scan, stream);
     if (rc) return rc;
     if (dtype == COL_F32)
-        emit_kernel<float><<<blocks, TRV_THREADS, 0, s>>>(pairs, capacity, base, counts, total, stash, (const float*)wide, (const float*)bounds, ids_sorted, n, q_begin, q_end);
+        emit_kernel<float><<<blocks, TRV_THREADS, 0, s>>>(pairs, capacity, base, counts, total, stash, w, (const float*)bounds, (const float*)scene2x4, ids_sorted, n, q_begin, q_end);
     else
-        emit_kernel<double><<<blocks, TRV_THREADS, 0, s>>>(pairs, capacity, base, counts, total, stash, (const double*)wide, (const double*)bounds, ids_sorted, n, q_begin, q_end);
+        emit_kernel<double><<<blocks, TRV_THREADS, 0, s>>>(pairs, capacity, base, counts, total, stash, w, (const double*)bounds, (const double*)scene2x4, ids_sorted, n, q_begin, q_end);
     COL_CHECK_LAUNCH();
     return 0;
 }
 
 COL_API int col_traverse_wide_write(uint32_t* pairs, uint64_t capacity, const uint32_t* offsets, uint64_t base,
-                                    const void* wide, const void* bounds, const uint32_t* ids_sorted, int dtype,
-                                    uint32_t n, uint32_t q_begin, uint32_t q_end, void* stream) {
-    if (!wide || !bounds || !ids_sorted || !offsets || bad_range(n, q_begin, q_end) || (!pairs && capacity))
+                                    const void* wide, const void* bounds, const void* scene2x4,
+                                    const uint32_t* ids_sorted, int dtype, uint32_t n, uint32_t q_begin,
+                                    uint32_t q_end, void* stream) {
+    if (!wide || !bounds || !scene2x4 || !ids_sorted || !offsets || bad_range(n, q_begin, q_end) || (!pairs && capacity))
         return COL_ERR_BAD_ARG;
+    if (dtype != COL_F32 && dtype != COL_F64) return COL_ERR_UNSUPPORTED;
     if (capacity == 0 || q_begin == q_end || n < 2) return 0;
     const unsigned blocks = col_blocks(q_end - q_begin, TRV_THREADS);
     cudaStream_t s = col_stream(stream);
+    const unsigned char* w = (const unsigned char*)wide;
     if (dtype == COL_F32)
-        write_kernel<float><<<blocks, TRV_THREADS, 0, s>>>(pairs, capacity, offsets, base, (const float*)wide, (const float*)bounds, ids_sorted, n, q_begin, q_end);
-    else if (dtype == COL_F64)
-        write_kernel<double><<<blocks, TRV_THREADS, 0, s>>>(pairs, capacity, offsets, base, (const double*)wide, (const double*)bounds, ids_sorted, n, q_begin, q_end);
+        write_kernel<float><<<blocks, TRV_THREADS, 0, s>>>(pairs, capacity, offsets, base, w, (const float*)bounds, (const float*)scene2x4, ids_sorted, n, q_begin, q_end);
     else
-        return COL_ERR_UNSUPPORTED;
+        write_kernel<double><<<blocks, TRV_THREADS, 0, s>>>(pairs, capacity, offsets, base, w, (const double*)bounds, (const double*)scene2x4, ids_sorted, n, q_begin, q_end);
     COL_CHECK_LAUNCH();
     return 0;
 }

@@ -26,14 +26,12 @@ __device__ __forceinline__ int delta(const uint32_t* __restrict__ codes, uint32_
     return ci != cj ? __clz(ci ^ cj) : 32 + __clz(i ^ j);
 }
 
-// WIDE: additionally write {child a, child b, right_edge a, right_edge b} into
-// the traversal node of i (see traverse_wide.cu): child a covers sorted leaves
-// [lo, gamma] and child b [gamma + 1, hi], so their right edges are gamma and hi.
+// WIDE: additionally write {child a, child b} into the 32-byte traversal record of i
+// (qnode.cuh) and initialise the refit's arrival word.
 template <bool LEAVES, bool WIDE>
 __global__ void __launch_bounds__(256)
 build_tree_kernel(const uint32_t* __restrict__ codes, const uint32_t* __restrict__ ids, col_node* __restrict__ nodes,
-                  uint32_t n, unsigned char* __restrict__ wide, uint32_t wide_stride, uint32_t wide_meta_off,
-                  uint32_t* __restrict__ flags) {
+                  uint32_t n, unsigned char* __restrict__ wide, uint32_t* __restrict__ flags) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const uint32_t leaf_start = n - 1;
@@ -80,7 +78,7 @@ build_tree_kernel(const uint32_t* __restrict__ codes, const uint32_t* __restrict
     nodes[child_a].parent = i;
     nodes[child_b].parent = i;
     if (WIDE) {
-        *reinterpret_cast<uint4*>(wide + (size_t)i * wide_stride + wide_meta_off) = make_uint4(child_a, child_b, gamma, hi);
+        *reinterpret_cast<uint2*>(wide + (size_t)i * 32) = make_uint2(child_a, child_b);
         // arrival word of the refit (refit.cu): marked when all leaves of the node lie in one
         // 256-leaf window, i.e. inside one refit block, which then resolves it in shared memory
         flags[i] = ((lo >> 8) == (hi >> 8)) ? 0x80000000u : 0u;
@@ -104,22 +102,20 @@ COL_API int col_build_tree(const uint32_t* codes_sorted, const uint32_t* ids_sor
     if (n > 0x80000000u) return COL_ERR_TOO_LARGE;
     const unsigned blocks = col_blocks(n, 256);
     if (ids_sorted)
-        build_tree_kernel<true, false><<<blocks, 256, 0, col_stream(stream)>>>(codes_sorted, ids_sorted, (col_node*)nodes, n, nullptr, 0, 0, nullptr);
+        build_tree_kernel<true, false><<<blocks, 256, 0, col_stream(stream)>>>(codes_sorted, ids_sorted, (col_node*)nodes, n, nullptr, nullptr);
     else
-        build_tree_kernel<false, false><<<blocks, 256, 0, col_stream(stream)>>>(codes_sorted, nullptr, (col_node*)nodes, n, nullptr, 0, 0, nullptr);
+        build_tree_kernel<false, false><<<blocks, 256, 0, col_stream(stream)>>>(codes_sorted, nullptr, (col_node*)nodes, n, nullptr, nullptr);
     COL_CHECK_LAUNCH();
     return 0;
 }
 
 COL_API int col_build_tree_wide(const uint32_t* codes_sorted, const uint32_t* ids_sorted, void* nodes, void* wide,
-                                uint32_t* flags, int dtype, uint32_t n, void* stream) {
+                                uint32_t* flags, uint32_t n, void* stream) {
     if (!codes_sorted || !ids_sorted || !nodes || !wide || !flags) return COL_ERR_BAD_ARG;
-    if (dtype != COL_F32 && dtype != COL_F64) return COL_ERR_UNSUPPORTED;
     if (n == 0) return 0;
     if (n > 0x80000000u) return COL_ERR_TOO_LARGE;
-    const uint32_t scalar = dtype == COL_F32 ? 4u : 8u;
     build_tree_kernel<true, true><<<col_blocks(n, 256), 256, 0, col_stream(stream)>>>(
-        codes_sorted, ids_sorted, (col_node*)nodes, n, (unsigned char*)wide, 16 * scalar, 12 * scalar, flags);
+        codes_sorted, ids_sorted, (col_node*)nodes, n, (unsigned char*)wide, flags);
     COL_CHECK_LAUNCH();
     return 0;
 }

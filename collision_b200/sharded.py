@@ -8,8 +8,8 @@ row totals are all-gathered so every rank knows the global count and its base
 offset.  Concatenating the ranks' lists in rank order gives exactly the 1-GPU
 (= sequential reference) list.
 
-What travels (per sphere): the traversal record 64 B + the leaf box 32 B + the
-sorted id 4 B = 100 B (f32); the Node array stays on rank 0.
+What travels (per sphere): the traversal record 32 B + the leaf box 32 B + the
+sorted id 4 B = 68 B (f32); the Node array stays on rank 0.
 
 The distributed plumbing (`shard_range`, `exchange_totals`, `broadcast_buffers`)
 is device-agnostic so that it is covered by world_size-2 gloo tests on CPU.
@@ -57,11 +57,11 @@ class ShardedCollider:
     def __init__(self, ctx, size, ngroups, group_size, coord_dtype=dtype('float32'), group=None, src=0,
                  mode="broadcast_tree"):
         """mode "broadcast_tree" (north_star): rank `src` sorts, builds and refits; the
-        traversal data (100 B per sphere) is broadcast.
+        traversal data (68 B per sphere) is broadcast.
         mode "replicate_build": the INPUT (coords + radii, 20 B per sphere) is broadcast
         from `src` and every rank builds the identical tree itself -- the build is
         deterministic and bit-exact, so the result is the same; it trades redundant
-        compute for 5x less NVLink traffic and no serial rank-0 phase."""
+        compute for 3.4x less NVLink traffic and no serial rank-0 phase."""
         if mode not in self.MODES:
             raise ValueError("mode must be one of {}".format(self.MODES))
         self.mode = mode
@@ -95,7 +95,7 @@ class ShardedCollider:
         n = c.size
         isz = c.program.coord_dtype.itemsize
         leaf_boxes = c._bounds_buf[(n - 1) * 8 * isz:(2 * n - 1) * 8 * isz]
-        return [c._wide_buf, leaf_boxes, c._ids_bufs[1][:n * 4]]
+        return [c._wide_buf, leaf_boxes, c._ids_bufs[1][:n * 4], c._scene_buf]
 
     def get_collisions(self, cq, coords_buf, radii_buf, n_collisions_buf, collisions_buf, n_collisions,
                        wait_for=None, sync_totals=True):

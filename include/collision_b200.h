@@ -160,35 +160,42 @@ int col_traverse_atomic(uint32_t* pairs, uint32_t* counter, uint32_t capacity, c
  * Collider itself (collision/collision.py:171-196: fillInternal, generateBVH,
  * leafBounds, internalBounds, traverse) runs on a traversal-oriented copy of the
  * tree that the build and refit kernels emit alongside the Node/Bound arrays:
- * one record of 16 scalars per internal node (64 B f32 / 128 B f64):
- *   [0..5] box of child a (lo xyz, hi xyz)   [6..11] box of child b
- *   [12..15] as 4 x u32 in the first 16 bytes: child a, child b,
- *            right_edge(child a), right_edge(child b)
- * `wide`: (n-1) such records.  `flags`: n-1 u32 arrival words, initialised by
- * col_build_tree_wide and consumed by col_refit_wide (call them as a pair).  `bounds` (Bound array) still receives every box;
- * the traversal reads only its leaf part (the query boxes).  The arithmetic and
- * the reported rows are identical to the entry points above.
+ * one 32-byte record per internal node (any coordinate dtype):
+ *   u32 child a, u32 child b, 6 x u16 box of child a, 6 x u16 box of child b
+ * The u16 boxes live on a 65536^3 grid over the scene bounds and are rounded
+ * OUTWARD, so an internal node is never pruned wrongly (a few extra nodes may be
+ * visited); whether a LEAF is reported is always decided on the exact float boxes
+ * of the Bound array, exactly as collision.cl:164-166 -- the reported rows and
+ * their order are identical to the entry points above.  A visit is one 256-bit load.
+ *
+ * `wide`: 32 * (n-1) bytes.  `flags`: n-1 u32 arrival words, initialised by
+ * col_build_tree_wide and consumed by col_refit_wide (call them as a pair).
+ * `scene2x4`: {min[4], max[4]} of the centres as written by col_bounds -- NOT slot
+ * 0 of `bounds` (the refit overwrites that with the root box).
  *
  * col_traverse_wide_pairs: one walk per query + deterministic compaction (walk
  * and park hits -> single-pass scan of the counts -> emit): row k of query q
  * lands at base + (number of rows of queries q_begin..q-1) + k when that index
  * is < capacity; *total_out (u64, required) = rows found in the range (the list
  * positions are exact for totals < 2^32 per call).  capacity == 0: count only.
- * scratch: col_traverse_scratch_bytes(q_end - q_begin).  ids_sorted: ids in sorted order (the sort's
- * payload output). */
+ * scratch: col_traverse_scratch_bytes(q_end - q_begin).
+ * ids_sorted: ids in sorted order (the sort's payload output). */
 int col_build_tree_wide(const uint32_t* codes_sorted, const uint32_t* ids_sorted, void* nodes, void* wide,
-                        uint32_t* flags, int dtype, uint32_t n, void* stream);
+                        uint32_t* flags, uint32_t n, void* stream);
 int col_refit_wide(void* bounds, void* wide, uint32_t* flags, const void* nodes, const void* coords4,
-                   const void* radii, int dtype, uint32_t n, void* stream);
+                   const void* radii, const void* scene2x4, int dtype, uint32_t n, void* stream);
 size_t col_traverse_scratch_bytes(uint32_t n_queries);
-int col_traverse_wide_count(uint64_t* total, uint32_t* counts, const void* wide, const void* bounds, int dtype,
-                            uint32_t n, uint32_t q_begin, uint32_t q_end, void* stream);
+int col_traverse_wide_count(uint64_t* total, uint32_t* counts, const void* wide, const void* bounds,
+                            const void* scene2x4, int dtype, uint32_t n, uint32_t q_begin, uint32_t q_end,
+                            void* stream);
 int col_traverse_wide_pairs(uint32_t* pairs, uint64_t capacity, uint64_t base, uint64_t* total_out,
-                            const void* wide, const void* bounds, const uint32_t* ids_sorted, int dtype,
-                            uint32_t n, uint32_t q_begin, uint32_t q_end, void* scratch, void* stream);
+                            const void* wide, const void* bounds, const void* scene2x4,
+                            const uint32_t* ids_sorted, int dtype, uint32_t n, uint32_t q_begin,
+                            uint32_t q_end, void* scratch, void* stream);
 int col_traverse_wide_write(uint32_t* pairs, uint64_t capacity, const uint32_t* offsets, uint64_t base,
-                            const void* wide, const void* bounds, const uint32_t* ids_sorted, int dtype,
-                            uint32_t n, uint32_t q_begin, uint32_t q_end, void* stream);
+                            const void* wide, const void* bounds, const void* scene2x4,
+                            const uint32_t* ids_sorted, int dtype, uint32_t n, uint32_t q_begin,
+                            uint32_t q_end, void* stream);
 
 /* ----------------------------------------------------------- find_offsets
  * Replaces OffsetFinder.find_offsets (collision/offset.py:40-49,

@@ -286,7 +286,7 @@ def test_wide_count_and_write_entry_points(cuda_env, oracle):
     for qb, qe in zip(bounds, bounds[1:]):
         counts = dev_empty((qe - qb) * 4)
         tot = torch.zeros(1, dtype=torch.int64, device=dev)
-        assert L.col_traverse_wide_count(P(tot), P(counts), P(col._wide_buf), P(col._bounds_buf), 0, n, qb, qe, S) == 0
+        assert L.col_traverse_wide_count(P(tot), P(counts), P(col._wide_buf), P(col._bounds_buf), P(col._scene_buf), 0, n, qb, qe, S) == 0
         cq.synchronize()
         cnt = to_host(counts, 'uint32', (qe - qb,))
         np.testing.assert_equal(cnt, want['counts'][qb:qe])
@@ -294,14 +294,14 @@ def test_wide_count_and_write_entry_points(cuda_env, oracle):
         offs = to_dev(oracle.exclusive_scan(cnt))
         out = dev_empty(max(int(cnt.sum()), 1) * 8)
         assert L.col_traverse_wide_write(P(out), int(cnt.sum()), P(offs), 0, P(col._wide_buf), P(col._bounds_buf),
-                                         P(col._ids_bufs[1]), 0, n, qb, qe, S) == 0
+                                         P(col._scene_buf), P(col._ids_bufs[1]), 0, n, qb, qe, S) == 0
         cq.synchronize()
         rows.append(to_host(out, 'uint32', (int(cnt.sum()), 2)))
         # fused over the same sub-range gives the same rows
         out2 = dev_empty(max(int(cnt.sum()), 1) * 8)
         scr = dev_empty(L.col_traverse_scratch_bytes(qe - qb))
         assert L.col_traverse_wide_pairs(P(out2), int(cnt.sum()), 0, P(tot), P(col._wide_buf), P(col._bounds_buf),
-                                         P(col._ids_bufs[1]), 0, n, qb, qe, P(scr), S) == 0
+                                         P(col._scene_buf), P(col._ids_bufs[1]), 0, n, qb, qe, P(scr), S) == 0
         cq.synchronize()
         np.testing.assert_equal(to_host(out2, 'uint32', (int(cnt.sum()), 2)), rows[-1])
         assert int(tot.item()) == int(cnt.sum())

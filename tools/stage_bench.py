@@ -115,12 +115,13 @@ def main():
     report("traverse write", T(lambda: L.col_traverse_write(P(pairs), m, P(col._counts_buf), 0, P(col._nodes_buf), P(col._bounds_buf), code, n, 0, n, S)), 36 * n + 8 * m)
     report("traverse atomic (count only)", T(lambda: L.col_traverse_atomic(None, P(n_buf), 0, P(col._nodes_buf), P(col._bounds_buf), code, n, 0, n, S)), 36 * n)
 
-    # ---- wide / fused path (the Collider's default)
-    report("build tree + wide meta", T(lambda: L.col_build_tree_wide(P(col._codes_bufs[1]), P(col._ids_bufs[1]), P(col._nodes_buf), P(col._wide_buf), P(col._flags_buf), code, n, S)), 60 * n)
-    report("leaf boxes + refit (wide)", T(lambda: L.col_refit_wide(P(col._bounds_buf), P(col._wide_buf), P(col._flags_buf), P(col._nodes_buf), P(coords), P(radii), code, n, S),
-                                          setup=lambda: L.col_build_tree_wide(P(col._codes_bufs[1]), P(col._ids_bufs[1]), P(col._nodes_buf), P(col._wide_buf), P(col._flags_buf), code, n, S)), 192 * n)
-    report("traverse wide count", T(lambda: L.col_traverse_wide_count(P(col._total_buf), None, P(col._wide_buf), P(col._bounds_buf), code, n, 0, n, S)), 36 * n)
-    report("traverse wide fused (write)", T(lambda: L.col_traverse_wide_pairs(P(pairs), m, 0, P(col._total_buf), P(col._wide_buf), P(col._bounds_buf), P(col._ids_bufs[1]), code, n, 0, n, P(col._trv_scratch), S)), 36 * n + 8 * m)
+    # ---- fast path (the Collider's default): 32-byte traversal records
+    L.col_bounds(P(coords), n, code, 4, P(col._scene_buf), P(rs), S)
+    report("build tree + wide meta", T(lambda: L.col_build_tree_wide(P(col._codes_bufs[1]), P(col._ids_bufs[1]), P(col._nodes_buf), P(col._wide_buf), P(col._flags_buf), n, S)), 60 * n)
+    report("leaf boxes + refit (wide)", T(lambda: L.col_refit_wide(P(col._bounds_buf), P(col._wide_buf), P(col._flags_buf), P(col._nodes_buf), P(coords), P(radii), P(col._scene_buf), code, n, S),
+                                          setup=lambda: L.col_build_tree_wide(P(col._codes_bufs[1]), P(col._ids_bufs[1]), P(col._nodes_buf), P(col._wide_buf), P(col._flags_buf), n, S)), 192 * n)
+    report("traverse wide count", T(lambda: L.col_traverse_wide_count(P(col._total_buf), None, P(col._wide_buf), P(col._bounds_buf), P(col._scene_buf), code, n, 0, n, S)), 36 * n)
+    report("traverse wide pairs (walk+scan+emit)", T(lambda: L.col_traverse_wide_pairs(P(pairs), m, 0, P(col._total_buf), P(col._wide_buf), P(col._bounds_buf), P(col._scene_buf), P(col._ids_bufs[1]), code, n, 0, n, P(col._trv_scratch), S)), 36 * n + 8 * m)
     torch.cuda.synchronize()
     assert int(col._total_buf.item()) == m, (int(col._total_buf.item()), m)
 
