@@ -241,7 +241,7 @@ class Collider:
                                              P(self._wide_buf), P(self._bounds_buf), P(self._scene_buf),
                                              P(self._ids_bufs[1]), self.program._code, self.size, q_begin, q_end,
                                              P(self._trv_scratch), S), "col_traverse_wide_pairs")
-        self._mark(cq, "traverse_pairs" if n_collisions else "traverse_count", 3 if n_collisions else 1)
+        self._mark(cq, "traverse_pairs" if n_collisions else "traverse_count", 4 if n_collisions else 1)
 
     def _traverse_fast(self, cq, coords_buf, radii_buf, n_collisions_buf, collisions_buf, n_collisions):
         self._build_wide(cq, coords_buf, radii_buf)

@@ -2,8 +2,11 @@
 //
 // One record per internal node (written by tree.cu + refit.cu, read by traverse_wide.cu):
 //   w0 = child a, w1 = child b,
-//   w2..w4 = box of child a, w5..w7 = box of child b, each as 6 x u16 {lo.x lo.y lo.z hi.x hi.y hi.z}
-// A visit is ONE 256-bit load.  The u16 coordinates live on a 65536^3 grid spanning the scene
+//   w2..w4 = box of child a, w5..w7 = box of child b, each as 6 x u16
+//             {lo.x lo.y | lo.z ~hi.x | ~hi.y ~hi.z}          (~v = 65535 - v)
+// A visit is ONE 256-bit load.  The query carries {hi.x hi.y | hi.z ~lo.x | ~lo.y ~lo.z}, so the
+// six comparisons of the box test all read "record half-word <= query half-word" and are
+// evaluated two at a time: max.u16x2(record, query) == query  (VIMNMX.U16x2 + ISETP).  The u16 coordinates live on a 65536^3 grid spanning the scene
 // bounds (of the centres; anything outside clamps to the border cells) and are rounded
 // OUTWARD (floor for lo, ceil for hi), the query box likewise, and compared with >= / <=:
 // an exact overlap always implies a grid overlap, so an internal node is never pruned
@@ -47,16 +50,37 @@ __device__ __forceinline__ uint32_t grid_ceil(float t) { return (uint32_t)__floa
 __device__ __forceinline__ uint32_t grid_floor(double t) { return (uint32_t)__double2int_rd(t); }
 __device__ __forceinline__ uint32_t grid_ceil(double t) { return (uint32_t)__double2int_ru(t); }
 
-// box {lo[3], hi[3]} -> 3 words of 6 x u16, rounded outward
+// box {lo[3], hi[3]} -> 3 words of 6 x u16 {lo.x lo.y | lo.z ~hi.x | ~hi.y ~hi.z}, rounded outward
 template <typename T>
 __device__ __forceinline__ uint3 quantise_box(const Quant<T>& qz, const T (&lo)[3], const T (&hi)[3]) {
     uint32_t v[6];
 #pragma unroll
     for (int k = 0; k < 3; k++) {
         v[k] = grid_floor(grid_coord(lo[k], qz.lo[k], qz.scale[k]));
-        v[3 + k] = grid_ceil(grid_coord(hi[k], qz.lo[k], qz.scale[k]));
+        v[3 + k] = 65535u - grid_ceil(grid_coord(hi[k], qz.lo[k], qz.scale[k]));
     }
     return make_uint3(v[0] | (v[1] << 16), v[2] | (v[3] << 16), v[4] | (v[5] << 16));
+}
+// the query's side of the same test: {hi.x hi.y | hi.z ~lo.x | ~lo.y ~lo.z}, rounded outward
+template <typename T>
+__device__ __forceinline__ uint3 quantise_query(const Quant<T>& qz, const T (&lo)[3], const T (&hi)[3]) {
+    uint32_t v[6];
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+        v[k] = grid_ceil(grid_coord(hi[k], qz.lo[k], qz.scale[k]));
+        v[3 + k] = 65535u - grid_floor(grid_coord(lo[k], qz.lo[k], qz.scale[k]));
+    }
+    return make_uint3(v[0] | (v[1] << 16), v[2] | (v[3] << 16), v[4] | (v[5] << 16));
+}
+__device__ __forceinline__ uint32_t max_u16x2(uint32_t a, uint32_t b) {
+    uint32_t d;
+    asm("max.u16x2 %0, %1, %2;" : "=r"(d) : "r"(a), "r"(b));
+    return d;
+}
+// every half-word of the record's box <= the query's  <=>  the grid boxes overlap
+__device__ __forceinline__ bool grid_overlap(const uint3& query, uint32_t r0, uint32_t r1, uint32_t r2) {
+    return (max_u16x2(r0, query.x) == query.x) & (max_u16x2(r1, query.y) == query.y) &
+           (max_u16x2(r2, query.z) == query.z);
 }
 
 constexpr uint32_t QNODE_BYTES = 32;

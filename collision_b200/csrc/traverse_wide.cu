@@ -18,6 +18,8 @@
 //    a second time, for the remainder.  (A single fused kernel chaining blocks by
 //    decoupled look-back was measured slower: blocks of dense regions stall every
 //    later block, and a shared-memory stash shrinks the L1 the walk depends on.)
+#include <cstdlib>
+
 #include "common.cuh"
 #include "qnode.cuh"
 
@@ -25,30 +27,30 @@ namespace {
 
 constexpr int TRV_THREADS = 128;
 constexpr int TRV_STASH = 32;
+constexpr uint32_t TRV_DONE = 0xFFFFFFFFu;   // stack sentinel / "lane has no node to visit"
 
-struct QNode {
-    uint32_t ca, cb;
-    uint32_t a[6], b[6];  // lo xyz, hi xyz on the u16 grid
-};
+struct QNode { uint32_t w[8]; };   // see qnode.cuh
 
 __device__ __forceinline__ QNode load_qnode(const unsigned char* __restrict__ wide, uint32_t idx) {
-    uint32_t w[8];
-    asm volatile("ld.global.nc.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
-                 : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]), "=r"(w[4]), "=r"(w[5]), "=r"(w[6]), "=r"(w[7])
-                 : "l"(wide + (size_t)idx * QNODE_BYTES));
     QNode q;
-    q.ca = w[0]; q.cb = w[1];
-    q.a[0] = w[2] & 0xFFFFu; q.a[1] = w[2] >> 16; q.a[2] = w[3] & 0xFFFFu;
-    q.a[3] = w[3] >> 16;     q.a[4] = w[4] & 0xFFFFu; q.a[5] = w[4] >> 16;
-    q.b[0] = w[5] & 0xFFFFu; q.b[1] = w[5] >> 16; q.b[2] = w[6] & 0xFFFFu;
-    q.b[3] = w[6] >> 16;     q.b[4] = w[7] & 0xFFFFu; q.b[5] = w[7] >> 16;
+#ifndef COL_QNODE_LD128   // (two 128-bit loads measured 3 % slower on B200)
+    asm volatile("ld.global.nc.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=r"(q.w[0]), "=r"(q.w[1]), "=r"(q.w[2]), "=r"(q.w[3]), "=r"(q.w[4]), "=r"(q.w[5]), "=r"(q.w[6]),
+                   "=r"(q.w[7])
+                 : "l"(wide + (size_t)idx * QNODE_BYTES));
+#else
+    const uint4* p = reinterpret_cast<const uint4*>(wide + (size_t)idx * QNODE_BYTES);
+    const uint4 a = __ldg(p), b = __ldg(p + 1);
+    q.w[0] = a.x; q.w[1] = a.y; q.w[2] = a.z; q.w[3] = a.w;
+    q.w[4] = b.x; q.w[5] = b.y; q.w[6] = b.z; q.w[7] = b.w;
+#endif
     return q;
 }
 
-// exact query box + its outward-rounded grid image
+// exact query box + its outward-rounded grid image (query side of the packed test)
 template <typename T> struct Query {
     T lo[3], hi[3];
-    uint32_t glo[3], ghi[3];
+    uint3 grid;
 };
 
 template <typename T> struct LeafBox { T lo[3], hi[3]; };
@@ -74,18 +76,11 @@ __device__ __forceinline__ Query<T> load_query(const T* __restrict__ bounds, uin
     for (int k = 0; k < 3; k++) {
         q.lo[k] = b.lo[k];
         q.hi[k] = b.hi[k];
-        q.glo[k] = grid_floor(grid_coord(b.lo[k], qz.lo[k], qz.scale[k]));
-        q.ghi[k] = grid_ceil(grid_coord(b.hi[k], qz.lo[k], qz.scale[k]));
     }
+    q.grid = quantise_query(qz, q.lo, q.hi);
     return q;
 }
 
-// conservative test on the grid (see qnode.cuh): never false when the exact boxes overlap
-template <typename T>
-__device__ __forceinline__ bool grid_overlap(const Query<T>& q, const uint32_t (&c)[6]) {
-    return (q.ghi[0] >= c[0]) & (q.glo[0] <= c[3]) & (q.ghi[1] >= c[1]) & (q.glo[1] <= c[4]) & (q.ghi[2] >= c[2]) &
-           (q.glo[2] <= c[5]);
-}
 // collision.cl:164-166: all(q.max > c.min & q.min < c.max), strict, x y z -- on the exact boxes
 template <typename T>
 __device__ __forceinline__ bool exact_overlap(const Query<T>& q, const LeafBox<T>& c) {
@@ -93,56 +88,54 @@ __device__ __forceinline__ bool exact_overlap(const Query<T>& q, const LeafBox<T
            (q.hi[2] > c.lo[2]) & (q.lo[2] < c.hi[2]);
 }
 
-// One DFS walk (collision.cl:174-226).  on_hit(leaf_position, k) is called for the k-th
-// reported leaf, in reference order.  Returns the number of hits.
-template <typename T, typename F>
+// One step of the DFS of collision.cl:174-226 at internal node `idx`: tests both children
+// conservatively on the grid and returns the next node (TRV_DONE when the stack ran empty).
+// Leaf children that pass are reported through on_leaf(leaf position), child a before child b:
+//   EXACT  -- only after the exact test on the float boxes (a report is a collision row);
+//   !EXACT -- as CANDIDATES, without touching the Bound array: the walk then has no
+//             data-dependent side branch at all and the exact test runs later, batched.
+template <bool EXACT, typename T, typename F>
+__device__ __forceinline__ uint32_t visit(const unsigned char* __restrict__ wide, const T* __restrict__ bounds,
+                                          const Query<T>& query, uint32_t q, uint32_t leaf_start, uint32_t idx,
+                                          uint32_t* stack, int& sp, F&& on_leaf) {
+    const QNode w = load_qnode(wide, idx);
+    const uint32_t ca = w.w[0], cb = w.w[1];
+    const bool la = ca >= leaf_start, lb = cb >= leaf_start;
+    // child a is a left child: its right edge is its own index (leaf: its position);
+    // child b's right edge is this node's, already known to be > q
+    const uint32_t ra = la ? ca - leaf_start : ca;
+    const bool oa = grid_overlap(query.grid, w.w[2], w.w[3], w.w[4]) && ra > q;
+    const bool ob = grid_overlap(query.grid, w.w[5], w.w[6], w.w[7]);
+    if (oa && la) {
+        if (!EXACT || exact_overlap(query, load_leaf_box(bounds, ca))) on_leaf(ca - leaf_start);
+    }
+    if (ob && lb) {
+        if (!EXACT || exact_overlap(query, load_leaf_box(bounds, cb))) on_leaf(cb - leaf_start);
+    }
+    const bool ta = oa && !la, tb = ob && !lb;
+    if (!ta && !tb) return stack[--sp];
+    if (ta && tb) stack[sp++] = cb;
+    return ta ? ca : cb;
+}
+
+// One whole walk of one query.  on_leaf(leaf position, k) for the k-th report, in
+// reference order.  Returns the number of reports.
+template <bool EXACT, typename T, typename F>
 __device__ __forceinline__ uint32_t walk(const unsigned char* __restrict__ wide, const T* __restrict__ bounds,
-                                         const Query<T>& query, uint32_t q, uint32_t leaf_start, F&& on_hit) {
+                                         const Query<T>& query, uint32_t q, uint32_t leaf_start, F&& on_leaf) {
     if (q >= leaf_start) return 0;  // the last sorted leaf has nothing to its right (every right_edge <= q)
     uint32_t stack[64];
     int sp = 0;
-    stack[sp++] = 0xFFFFFFFFu;
+    stack[sp++] = TRV_DONE;
     uint32_t idx = 0, hits = 0;
     do {
-        const QNode w = load_qnode(wide, idx);
-        const bool la = w.ca >= leaf_start, lb = w.cb >= leaf_start;
-        // child a is a left child: its right edge is its own index (leaf: its position);
-        // child b's right edge is this node's, already known to be > q
-        const uint32_t ra = la ? w.ca - leaf_start : w.ca;
-        bool oa = grid_overlap(query, w.a) && ra > q;
-        bool ob = grid_overlap(query, w.b);
-        if (oa && la) {
-            if (exact_overlap(query, load_leaf_box(bounds, w.ca))) { on_hit(w.ca - leaf_start, hits); hits++; }
-        }
-        if (ob && lb) {
-            if (exact_overlap(query, load_leaf_box(bounds, w.cb))) { on_hit(w.cb - leaf_start, hits); hits++; }
-        }
-        const bool ta = oa && !la, tb = ob && !lb;
-        if (!ta && !tb) {
-            idx = stack[--sp];
-        } else {
-            idx = ta ? w.ca : w.cb;
-            if (ta && tb) stack[sp++] = w.cb;
-        }
-    } while (idx != 0xFFFFFFFFu);
+        idx = visit<EXACT>(wide, bounds, query, q, leaf_start, idx, stack, sp, [&](uint32_t pos) { on_leaf(pos, hits); hits++; });
+    } while (idx != TRV_DONE);
     return hits;
 }
 
-// ---- count only: per-block sum -> one atomic per block ----------------------
-template <typename T>
-__global__ void __launch_bounds__(TRV_THREADS)
-count_kernel(unsigned long long* __restrict__ total, uint32_t* __restrict__ counts, const unsigned char* __restrict__ wide,
-             const T* __restrict__ bounds, const T* __restrict__ scene, uint32_t n, uint32_t q_begin, uint32_t q_end) {
-    const uint32_t q = q_begin + blockIdx.x * TRV_THREADS + threadIdx.x;
-    const uint32_t leaf_start = n - 1;
-    uint32_t hits = 0;
-    if (q < q_end) {
-        const Query<T> query = load_query(bounds, leaf_start + q, make_quant(scene));
-        hits = walk(wide, bounds, query, q, leaf_start, [](uint32_t, uint32_t) {});
-        if (counts) counts[q - q_begin] = hits;
-    }
-    __shared__ uint32_t s_sum[TRV_THREADS / 32];
-    uint32_t v = hits;
+__device__ __forceinline__ void block_add(unsigned long long* total, unsigned long long v) {
+    __shared__ unsigned long long s_sum[TRV_THREADS / 32];
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
     if (lane_id() == 0) s_sum[threadIdx.x >> 5] = v;
@@ -154,41 +147,92 @@ count_kernel(unsigned long long* __restrict__ total, uint32_t* __restrict__ coun
     }
 }
 
-// ---- walk once: per-query counts + parked hits ---------------------------------
-// Every query walks ONCE.  Its hit count goes to counts[], its first TRV_STASH hits
-// (sorted leaf positions) are parked in a k-major global array stash[k * nq + i]:
-// lanes of a warp park their k-th hit in one 128-byte row, and only rows that
-// are actually used ever move.  No inter-block dependency, so dense and sparse
-// regions of the scene do not stall each other.
+// ---- count only ---------------------------------------------------------------
 template <typename T>
 __global__ void __launch_bounds__(TRV_THREADS)
-walk_park_kernel(unsigned long long* __restrict__ total, uint32_t* __restrict__ counts, uint32_t* __restrict__ stash,
-                 const unsigned char* __restrict__ wide, const T* __restrict__ bounds, const T* __restrict__ scene,
-                 uint32_t n, uint32_t q_begin, uint32_t q_end) {
-    const uint32_t i = blockIdx.x * TRV_THREADS + threadIdx.x;
-    const uint32_t q = q_begin + i;
-    const uint32_t nq = q_end - q_begin;
-    const uint32_t leaf_start = n - 1;
+count_kernel(unsigned long long* __restrict__ total, uint32_t* __restrict__ counts,
+             const unsigned char* __restrict__ wide, const T* __restrict__ bounds, const T* __restrict__ scene,
+             uint32_t n, uint32_t q_begin, uint32_t q_end) {
+    const uint32_t q = q_begin + blockIdx.x * TRV_THREADS + threadIdx.x;
     uint32_t hits = 0;
     if (q < q_end) {
+        const uint32_t leaf_start = n - 1;
         const Query<T> query = load_query(bounds, leaf_start + q, make_quant(scene));
-        uint32_t* park = stash + i;
-        hits = walk(wide, bounds, query, q, leaf_start, [park, nq](uint32_t pos, uint32_t k) {
-            if (k < TRV_STASH) park[(size_t)k * nq] = pos;
-        });
-        counts[i] = hits;
+        hits = walk<true>(wide, bounds, query, q, leaf_start, [](uint32_t, uint32_t) {});
+        if (counts) counts[q - q_begin] = hits;
     }
-    __shared__ uint32_t s_sum[TRV_THREADS / 32];
-    uint32_t v = hits;
+    block_add(total, hits);
+}
+
+// ---- walk once: candidates ------------------------------------------------------
+// Every query walks ONCE, on the traversal records only.  The leaves whose grid boxes
+// overlap the query's are CANDIDATES: their number goes to counts[], the first TRV_STASH
+// of them (sorted leaf positions, in reference order) are parked in a k-major global
+// array stash[k * nq + i]: lanes of a warp park their k-th candidate in one 128-byte row,
+// and only rows that are actually used ever move.  No inter-block dependency, so dense
+// and sparse regions of the scene do not stall each other.
+template <typename T>
+__global__ void __launch_bounds__(TRV_THREADS)
+candidates_kernel(uint32_t* __restrict__ counts, uint32_t* __restrict__ stash, const unsigned char* __restrict__ wide,
+                  const T* __restrict__ bounds, const T* __restrict__ scene, uint32_t n, uint32_t q_begin,
+                  uint32_t q_end, uint32_t prefetch_lines) {
+    const uint32_t nq = q_end - q_begin;
+    const uint32_t i = blockIdx.x * TRV_THREADS + threadIdx.x;
+    {   // the low levels of the walks of this block live in the records right of its first query
+        const uint32_t first = q_begin + blockIdx.x * TRV_THREADS;
+        const uint32_t rec = first + threadIdx.x * 4;  // one 128-byte line (4 records) per thread
+        if (threadIdx.x < prefetch_lines && rec < n - 1)
+            asm volatile("prefetch.global.L1 [%0];" ::"l"(wide + (size_t)rec * QNODE_BYTES));
+    }
+    if (i >= nq) return;
+    const uint32_t q = q_begin + i, leaf_start = n - 1;
+    const Query<T> query = load_query(bounds, leaf_start + q, make_quant(scene));
+    uint32_t* park = stash + i;
+    counts[i] = walk<false>(wide, bounds, query, q, leaf_start, [park, nq](uint32_t pos, uint32_t k) {
+        if (k < TRV_STASH) park[(size_t)k * nq] = pos;
+    });
+}
+
+// ---- confirm: candidates -> collision rows ----------------------------------------
+// The exact test of collision.cl:164-166 on the float boxes, batched: thread i runs over
+// its parked candidates (coalesced k-major rows), keeps the confirmed ones in place (same
+// order) and replaces counts[i] by the number of rows of the query.  A query with more
+// than TRV_STASH candidates walks again, exactly, parking its first TRV_STASH rows.
+template <typename T>
+__global__ void __launch_bounds__(TRV_THREADS)
+confirm_kernel(unsigned long long* __restrict__ total, uint32_t* __restrict__ counts, uint32_t* __restrict__ stash,
+               const unsigned char* __restrict__ wide, const T* __restrict__ bounds, const T* __restrict__ scene,
+               uint32_t n, uint32_t q_begin, uint32_t q_end) {
+    const uint32_t nq = q_end - q_begin;
+    const uint32_t i = blockIdx.x * TRV_THREADS + threadIdx.x;
+    uint32_t hits = 0;
+    if (i < nq) {
+        const uint32_t cand = counts[i];
+        if (cand) {
+            const uint32_t q = q_begin + i, leaf_start = n - 1;
+            uint32_t* park = stash + i;
+            if (cand <= TRV_STASH) {
+                const LeafBox<T> b = load_leaf_box(bounds, leaf_start + q);
+                Query<T> query;
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-    if (lane_id() == 0) s_sum[threadIdx.x >> 5] = v;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        unsigned long long t = 0;
-        for (int w = 0; w < TRV_THREADS / 32; w++) t += s_sum[w];
-        if (t) atomicAdd(total, t);
+                for (int k = 0; k < 3; k++) { query.lo[k] = b.lo[k]; query.hi[k] = b.hi[k]; }
+                for (uint32_t k = 0; k < cand; k++) {
+                    const uint32_t pos = park[(size_t)k * nq];
+                    if (exact_overlap(query, load_leaf_box(bounds, leaf_start + pos))) {
+                        park[(size_t)hits * nq] = pos;
+                        hits++;
+                    }
+                }
+            } else {
+                const Query<T> query = load_query(bounds, leaf_start + q, make_quant(scene));
+                hits = walk<true>(wide, bounds, query, q, leaf_start, [park, nq](uint32_t pos, uint32_t k) {
+                    if (k < TRV_STASH) park[(size_t)k * nq] = pos;
+                });
+            }
+            counts[i] = hits;
+        }
     }
+    block_add(total, hits);
 }
 
 // ---- emit: rows to their final, deterministic positions -----------------------
@@ -221,7 +265,7 @@ emit_kernel(uint32_t* __restrict__ pairs, uint64_t capacity, uint64_t base, cons
     if (hits > TRV_STASH) {
         const uint32_t leaf_start = n - 1;
         const Query<T> query = load_query(bounds, leaf_start + q, make_quant(scene));
-        walk(wide, bounds, query, q, leaf_start, [=](uint32_t pos, uint32_t k) {
+        walk<true>(wide, bounds, query, q, leaf_start, [=](uint32_t pos, uint32_t k) {
             const uint64_t at = out + k;
             if (k >= TRV_STASH && at < capacity)
                 *reinterpret_cast<uint2*>(pairs + at * 2) = make_uint2(qid, __ldg(ids + pos));
@@ -242,7 +286,7 @@ write_kernel(uint32_t* __restrict__ pairs, uint64_t capacity, const uint32_t* __
     if (out >= capacity) return;
     const Query<T> query = load_query(bounds, leaf_start + q, make_quant(scene));
     const uint32_t qid = __ldg(ids + q);
-    walk(wide, bounds, query, q, leaf_start, [=](uint32_t pos, uint32_t k) {
+    walk<true>(wide, bounds, query, q, leaf_start, [=](uint32_t pos, uint32_t k) {
         const uint64_t at = out + k;
         if (at < capacity) *reinterpret_cast<uint2*>(pairs + at * 2) = make_uint2(qid, __ldg(ids + pos));
     });
@@ -285,6 +329,28 @@ COL_API int col_traverse_wide_count(uint64_t* total, uint32_t* counts, const voi
     return 0;
 }
 
+template <typename T>
+static int pairs_impl(uint32_t* pairs, uint64_t capacity, uint64_t base, unsigned long long* total,
+                      const unsigned char* w, const T* bounds, const T* scene, const uint32_t* ids, uint32_t n,
+                      uint32_t q_begin, uint32_t q_end, char* sc, void* stream) {
+    cudaStream_t s = col_stream(stream);
+    const uint32_t nq = q_end - q_begin;
+    const PairsLayout L = pairs_layout(nq);
+    uint32_t* counts = reinterpret_cast<uint32_t*>(sc + L.counts);
+    uint32_t* stash = reinterpret_cast<uint32_t*>(sc + L.stash);
+    const unsigned blocks = col_blocks(nq, TRV_THREADS);
+    static const uint32_t pf = getenv("COL_TRV_PF") ? atoi(getenv("COL_TRV_PF")) : 64;
+    candidates_kernel<T><<<blocks, TRV_THREADS, 0, s>>>(counts, stash, w, bounds, scene, n, q_begin, q_end, pf);
+    COL_CHECK_LAUNCH();
+    confirm_kernel<T><<<blocks, TRV_THREADS, 0, s>>>(total, counts, stash, w, bounds, scene, n, q_begin, q_end);
+    COL_CHECK_LAUNCH();
+    const int rc = col_exclusive_scan_u32(counts, nq, nullptr, sc + L.scan, stream);
+    if (rc) return rc;
+    emit_kernel<T><<<blocks, TRV_THREADS, 0, s>>>(pairs, capacity, base, counts, total, stash, w, bounds, scene, ids, n, q_begin, q_end);
+    COL_CHECK_LAUNCH();
+    return 0;
+}
+
 COL_API int col_traverse_wide_pairs(uint32_t* pairs, uint64_t capacity, uint64_t base, uint64_t* total_out,
                                     const void* wide, const void* bounds, const void* scene2x4,
                                     const uint32_t* ids_sorted, int dtype, uint32_t n, uint32_t q_begin,
@@ -295,30 +361,14 @@ COL_API int col_traverse_wide_pairs(uint32_t* pairs, uint64_t capacity, uint64_t
     if (dtype != COL_F32 && dtype != COL_F64) return COL_ERR_UNSUPPORTED;
     if (capacity == 0)
         return col_traverse_wide_count(total_out, nullptr, wide, bounds, scene2x4, dtype, n, q_begin, q_end, stream);
-    cudaStream_t s = col_stream(stream);
-    COL_CUDA(cudaMemsetAsync(total_out, 0, sizeof(uint64_t), s));
+    COL_CUDA(cudaMemsetAsync(total_out, 0, sizeof(uint64_t), col_stream(stream)));
     if (q_begin == q_end || n < 2) return 0;
-    const uint32_t nq = q_end - q_begin;
-    const PairsLayout L = pairs_layout(nq);
-    char* sc = reinterpret_cast<char*>(scratch);
-    uint32_t* counts = reinterpret_cast<uint32_t*>(sc + L.counts);
-    uint32_t* stash = reinterpret_cast<uint32_t*>(sc + L.stash);
     unsigned long long* total = reinterpret_cast<unsigned long long*>(total_out);
-    const unsigned blocks = col_blocks(nq, TRV_THREADS);
     const unsigned char* w = (const unsigned char*)wide;
+    char* sc = reinterpret_cast<char*>(scratch);
     if (dtype == COL_F32)
-        walk_park_kernel<float><<<blocks, TRV_THREADS, 0, s>>>(total, counts, stash, w, (const float*)bounds, (const float*)scene2x4, n, q_begin, q_end);
-    else
-        walk_park_kernel<double><<<blocks, TRV_THREADS, 0, s>>>(total, counts, stash, w, (const double*)bounds, (const double*)scene2x4, n, q_begin, q_end);
-    COL_CHECK_LAUNCH();
-    const int rc = col_exclusive_scan_u32(counts, nq, nullptr, sc + L.scan, stream);
-    if (rc) return rc;
-    if (dtype == COL_F32)
-        emit_kernel<float><<<blocks, TRV_THREADS, 0, s>>>(pairs, capacity, base, counts, total, stash, w, (const float*)bounds, (const float*)scene2x4, ids_sorted, n, q_begin, q_end);
-    else
-        emit_kernel<double><<<blocks, TRV_THREADS, 0, s>>>(pairs, capacity, base, counts, total, stash, w, (const double*)bounds, (const double*)scene2x4, ids_sorted, n, q_begin, q_end);
-    COL_CHECK_LAUNCH();
-    return 0;
+        return pairs_impl<float>(pairs, capacity, base, total, w, (const float*)bounds, (const float*)scene2x4, ids_sorted, n, q_begin, q_end, sc, stream);
+    return pairs_impl<double>(pairs, capacity, base, total, w, (const double*)bounds, (const double*)scene2x4, ids_sorted, n, q_begin, q_end, sc, stream);
 }
 
 COL_API int col_traverse_wide_write(uint32_t* pairs, uint64_t capacity, const uint32_t* offsets, uint64_t base,

@@ -161,7 +161,9 @@ int col_traverse_atomic(uint32_t* pairs, uint32_t* counter, uint32_t capacity, c
  * leafBounds, internalBounds, traverse) runs on a traversal-oriented copy of the
  * tree that the build and refit kernels emit alongside the Node/Bound arrays:
  * one 32-byte record per internal node (any coordinate dtype):
- *   u32 child a, u32 child b, 6 x u16 box of child a, 6 x u16 box of child b
+ *   u32 child a, u32 child b, 6 x u16 box of child a, 6 x u16 box of child b,
+ *   each box as {lo.x lo.y | lo.z ~hi.x | ~hi.y ~hi.z} (~v = 65535 - v) so that the box
+ *   test is three packed "record <= query" comparisons (max.u16x2)
  * The u16 boxes live on a 65536^3 grid over the scene bounds and are rounded
  * OUTWARD, so an internal node is never pruned wrongly (a few extra nodes may be
  * visited); whether a LEAF is reported is always decided on the exact float boxes
