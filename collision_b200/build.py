@@ -49,11 +49,12 @@ def build(force=False, verbose=False):
     headers = list(CSRC.glob("*.cuh")) + [HERE.parent / "include" / "collision_b200.h", Path(__file__)]
     OBJ.mkdir(exist_ok=True)
     nvcc = _nvcc()
+    extra = os.environ.get("COL_NVCC_EXTRA", "").split()   # tuning aid (e.g. -DCOL_SORT_THREADS=256)
     jobs = []
     for src in sources():
         obj = OBJ / (src.stem + ".o")
         if force or _stale(obj, [src] + headers):
-            jobs.append([nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-c", str(src), "-o", str(obj)])
+            jobs.append([nvcc] + NVCC_FLAGS + extra + (["-Xptxas", "-v"] if verbose else []) + ["-c", str(src), "-o", str(obj)])
 
     def run(cmd):
         r = subprocess.run(cmd, capture_output=True, text=True)

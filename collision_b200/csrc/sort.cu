@@ -30,7 +30,13 @@ constexpr int RADIX_BITS = 8;
 constexpr int RADIX = 1 << RADIX_BITS;
 constexpr int MAX_PASSES = 8;
 
-constexpr int SORT_THREADS = 512;
+#ifndef COL_SORT_THREADS
+#define COL_SORT_THREADS 512
+#endif
+#ifndef COL_SORT_CTAS
+#define COL_SORT_CTAS 2
+#endif
+constexpr int SORT_THREADS = COL_SORT_THREADS;
 constexpr int SORT_WARPS = SORT_THREADS / 32;
 
 constexpr uint32_t ST_PARTIAL = 1u << 30;
@@ -92,100 +98,97 @@ __global__ void __launch_bounds__(RADIX) digit_base_kernel(uint32_t* ghist) {
 }
 
 // ----------------------------------------------------------------- onesweep
-template <typename K, bool HAS_VALUES, int RANK>
-__global__ void __launch_bounds__(SORT_THREADS, 2)
-onesweep_kernel(const K* __restrict__ keys_in, K* __restrict__ keys_out, const uint32_t* __restrict__ vals_in,
-                uint32_t* __restrict__ vals_out, uint32_t n, const uint32_t* __restrict__ digit_base,
-                uint32_t* __restrict__ status, unsigned* ticket, uint32_t shift, uint32_t mask) {
-    constexpr int ITEMS = Tile<K>::ITEMS;
+// Instruction budget notes (B200: the integer ALU pipe issues one warp instruction every
+// 2 cycles per scheduler, POPC/FLO one every 8 -- the ranking below is written against
+// that, not against the issue rate):
+//  * peers of a key = lanes of its row with the same digit: one VOTE per digit bit;
+//  * a lane's rank among its peers needs ONE popc (peers below me); the group's size is
+//    that popc + 1 on the highest peer, which alone bumps the warp's digit counter;
+//  * the counters hold BYTE offsets, and every per-(warp, digit) table sits at a constant
+//    displacement from the counter, so one address per key serves every lookup.
+// lanes of the warp whose 8-bit digit equals mine: one ballot per digit bit, four
+// instructions each (test, vote, select, combine) -- spelled out in PTX because the compiler's
+// own rendering of the obvious C loop spends six.
+__device__ __forceinline__ unsigned match_digit(uint32_t d) {
+    unsigned p;
+    asm(
+        "{\n"
+        ".reg .pred q;\n"
+        ".reg .b32 v, m, t;\n"
+        "and.b32 t, %1, 1;   setp.ne.u32 q, t, 0; vote.sync.ballot.b32 v, q, 0xffffffff; selp.b32 m, 0, 0xffffffff, q; xor.b32 %0, v, m;\n"
+        "and.b32 t, %1, 2;   setp.ne.u32 q, t, 0; vote.sync.ballot.b32 v, q, 0xffffffff; selp.b32 m, 0, 0xffffffff, q; lop3.b32 %0, %0, v, m, 0x60;\n"
+        "and.b32 t, %1, 4;   setp.ne.u32 q, t, 0; vote.sync.ballot.b32 v, q, 0xffffffff; selp.b32 m, 0, 0xffffffff, q; lop3.b32 %0, %0, v, m, 0x60;\n"
+        "and.b32 t, %1, 8;   setp.ne.u32 q, t, 0; vote.sync.ballot.b32 v, q, 0xffffffff; selp.b32 m, 0, 0xffffffff, q; lop3.b32 %0, %0, v, m, 0x60;\n"
+        "and.b32 t, %1, 16;  setp.ne.u32 q, t, 0; vote.sync.ballot.b32 v, q, 0xffffffff; selp.b32 m, 0, 0xffffffff, q; lop3.b32 %0, %0, v, m, 0x60;\n"
+        "and.b32 t, %1, 32;  setp.ne.u32 q, t, 0; vote.sync.ballot.b32 v, q, 0xffffffff; selp.b32 m, 0, 0xffffffff, q; lop3.b32 %0, %0, v, m, 0x60;\n"
+        "and.b32 t, %1, 64;  setp.ne.u32 q, t, 0; vote.sync.ballot.b32 v, q, 0xffffffff; selp.b32 m, 0, 0xffffffff, q; lop3.b32 %0, %0, v, m, 0x60;\n"
+        "and.b32 t, %1, 128; setp.ne.u32 q, t, 0; vote.sync.ballot.b32 v, q, 0xffffffff; selp.b32 m, 0, 0xffffffff, q; lop3.b32 %0, %0, v, m, 0x60;\n"
+        "}\n"
+        : "=r"(p)
+        : "r"(d));
+    return p;
+}
+
+template <typename K, int ITEMS, bool FULL, bool HAS_VALUES>
+__device__ __forceinline__ void onesweep_tile(const K* __restrict__ keys_in, K* __restrict__ keys_out,
+                                              const uint32_t* __restrict__ vals_in, uint32_t* __restrict__ vals_out,
+                                              uint32_t n, const uint32_t* __restrict__ digit_base,
+                                              uint32_t* __restrict__ status, uint32_t shift, uint32_t mask,
+                                              uint32_t bits, unsigned tile, unsigned char* smem_raw,
+                                              uint32_t* s_digit_start, uint32_t* s_global_off, uint32_t* s_scan_warp) {
     constexpr int TILE = SORT_THREADS * ITEMS;
     constexpr int WARP_ITEMS = 32 * ITEMS;
-
-    extern __shared__ __align__(16) unsigned char smem_raw[];
+    constexpr uint32_t KB = sizeof(K);
     K* s_keys = reinterpret_cast<K*>(smem_raw);                                     // TILE keys
     uint32_t* s_whist = reinterpret_cast<uint32_t*>(smem_raw + sizeof(K) * TILE);   // SORT_WARPS x RADIX
     uint32_t* s_vals = s_whist + SORT_WARPS * RADIX;                                // TILE values (if any)
-    __shared__ uint32_t s_digit_start[RADIX];
-    __shared__ uint32_t s_global_off[RADIX];
-    __shared__ uint32_t s_scan_warp[RADIX / 32];
-    __shared__ unsigned s_tile;
 
-    if (threadIdx.x == 0) s_tile = atomicAdd(ticket, 1u);
-    for (int i = threadIdx.x; i < SORT_WARPS * RADIX; i += SORT_THREADS) s_whist[i] = 0;
-    __syncthreads();
-    const unsigned tile = s_tile;
     const uint32_t tile_base = tile * (uint32_t)TILE;
-    const uint32_t valid = min((uint32_t)TILE, n - tile_base);
+    const uint32_t valid = FULL ? (uint32_t)TILE : n - tile_base;
     const unsigned warp = threadIdx.x >> 5, lane = lane_id();
     const uint32_t warp_off = warp * WARP_ITEMS;
 
     // ---- load (warp-striped: row i of a warp is 32 consecutive keys)
     K key[ITEMS];
+    {
+        const K* src = keys_in + tile_base + warp_off + lane;
 #pragma unroll
-    for (int i = 0; i < ITEMS; i++) {
-        const uint32_t e = warp_off + i * 32 + lane;
-        key[i] = e < valid ? keys_in[tile_base + e] : (K)~(K)0;  // padding sorts last within the tile
-    }
-
-    // ---- rank inside the warp (stable): peers = lanes of this row holding the
-    // same digit; the highest peer bumps the warp's digit counter once for all of
-    // them (an ordered shared-memory atomic, no warp barrier needed), every peer
-    // ranks itself by the number of lower peers.  All the match operations are
-    // issued before any of the dependent counter updates so their latencies overlap.
-    uint32_t* my_hist = s_whist + warp * RADIX;
-    uint16_t rank[ITEMS];
-    const unsigned lt = lanemask_lt();
-    unsigned peers[ITEMS];
-#pragma unroll
-    for (int i = 0; i < ITEMS; i++) {
-        const uint32_t d = (uint32_t)(key[i] >> shift) & mask;
-        if (RANK == 2) {  // ballot multi-split over the 8 digit bits
-            unsigned p = 0xffffffffu;
-#pragma unroll
-            for (int b = 0; b < RADIX_BITS; b++) {
-                const unsigned vote = __ballot_sync(0xffffffffu, (d >> b) & 1u);
-                p &= ((d >> b) & 1u) ? vote : ~vote;
-            }
-            peers[i] = p;
-        } else {
-            peers[i] = __match_any_sync(0xffffffffu, d);
+        for (int i = 0; i < ITEMS; i++) {
+            if (FULL) key[i] = src[i * 32];
+            else key[i] = (warp_off + i * 32 + lane) < valid ? src[i * 32] : (K)~(K)0;  // padding sorts last
         }
     }
+
+    // ---- early counts: per-warp digit histograms (byte units) by non-returning shared atomics
+    unsigned char* my_hist = reinterpret_cast<unsigned char*>(s_whist + warp * RADIX);
 #pragma unroll
     for (int i = 0; i < ITEMS; i++) {
         const uint32_t d = (uint32_t)(key[i] >> shift) & mask;
-        const int leader = 31 - __clz(peers[i]);
-        uint32_t before = 0;
-        if ((int)lane == leader) before = atomicAdd(&my_hist[d], (uint32_t)__popc(peers[i]));
-        before = __shfl_sync(0xffffffffu, before, leader);
-        rank[i] = (uint16_t)(before + __popc(peers[i] & lt));
+        atomicAdd(reinterpret_cast<uint32_t*>(my_hist + d * 4), KB);
     }
     // payload loads are issued here so that their latency hides behind the combine phase
     uint32_t val[HAS_VALUES ? ITEMS : 1];
     if (HAS_VALUES) {
+        const uint32_t* src = vals_in + tile_base + warp_off + lane;
 #pragma unroll
         for (int i = 0; i < ITEMS; i++) {
-            const uint32_t e = warp_off + i * 32 + lane;
-            val[i] = e < valid ? vals_in[tile_base + e] : 0u;
+            if (FULL) val[i] = src[i * 32];
+            else val[i] = (warp_off + i * 32 + lane) < valid ? src[i * 32] : 0u;
         }
     }
     __syncthreads();
 
-    // ---- combine warps: per digit, exclusive prefix over warps + tile count
+    // ---- combine warps: tile count per digit -> published at once (later tiles wait on it);
+    // exclusive scan over digits and over warps -> s_whist[w][d] = byte offset, in the sorted
+    // tile, of the first key of warp w with digit d
     uint32_t real = 0;  // number of real (non-padding) keys of digit threadIdx.x in this tile
     if (threadIdx.x < RADIX) {
         uint32_t padded = 0;
 #pragma unroll
-        for (int w = 0; w < SORT_WARPS; w++) {
-            const uint32_t c = s_whist[w * RADIX + threadIdx.x];
-            s_whist[w * RADIX + threadIdx.x] = padded;
-            padded += c;
-        }
+        for (int w = 0; w < SORT_WARPS; w++) padded += s_whist[w * RADIX + threadIdx.x];
         // the padding keys of a partial tile all carry the all-ones digit
-        real = padded - ((threadIdx.x == mask) ? (uint32_t)TILE - valid : 0u);
-        // publish as early as possible: later tiles are waiting on this
+        real = padded / KB - ((!FULL && threadIdx.x == mask) ? (uint32_t)TILE - valid : 0u);
         st_relaxed_u32(status + (size_t)tile * RADIX + threadIdx.x, (tile == 0 ? ST_INCLUSIVE : ST_PARTIAL) | real);
-        // exclusive scan of the 256 padded counts -> first tile rank of each digit
         uint32_t inc = padded;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
@@ -199,34 +202,66 @@ onesweep_kernel(const K* __restrict__ keys_in, K* __restrict__ keys_out, const u
     if (threadIdx.x < RADIX) {
         uint32_t base = 0;
         for (int w = 0; w < (int)warp; w++) base += s_scan_warp[w];
-        s_digit_start[threadIdx.x] += base;
+        base += s_digit_start[threadIdx.x];
+        s_digit_start[threadIdx.x] = base;
+#pragma unroll
+        for (int w = 0; w < SORT_WARPS; w++) {
+            const uint32_t c = s_whist[w * RADIX + threadIdx.x];
+            s_whist[w * RADIX + threadIdx.x] = base;
+            base += c;
+        }
     }
     __syncthreads();
 
-    // ---- scatter keys into shared memory in tile-rank order
+    // ---- rank inside the warp (stable: lane order within a row, rows in order) and move the
+    // key (and payload) to its place in the sorted tile.  The counter of (warp, digit) is the
+    // byte offset of the next key of that warp and digit: all peers read it, then the highest
+    // peer alone advances it.
+    const unsigned lt = lanemask_lt();
 #pragma unroll
     for (int i = 0; i < ITEMS; i++) {
         const uint32_t d = (uint32_t)(key[i] >> shift) & mask;
-        const uint32_t r = s_digit_start[d] + my_hist[d] + rank[i];
-        rank[i] = (uint16_t)r;
-        s_keys[r] = key[i];
+        const unsigned peers = match_digit(d);   // (narrower digits just vote on zero bits)
+        const uint32_t below = (uint32_t)__popc(peers & lt) * KB;  // bytes of my peers below me
+        uint32_t* ctr = reinterpret_cast<uint32_t*>(my_hist + d * 4);
+        const uint32_t r = *reinterpret_cast<volatile uint32_t*>(ctr) + below;
+        __syncwarp();
+        if ((peers >> lane) == 1u) *reinterpret_cast<volatile uint32_t*>(ctr) = r + KB;
+        __syncwarp();
+        *reinterpret_cast<K*>(reinterpret_cast<unsigned char*>(s_keys) + r) = key[i];
+        if (HAS_VALUES) *reinterpret_cast<uint32_t*>(reinterpret_cast<unsigned char*>(s_vals) + r / (KB / 4)) = val[i];
     }
 
-    // ---- decoupled look-back, one thread per digit
-    if (threadIdx.x < RADIX) {
+    // ---- decoupled look-back.  The tile's counts went out before the ranking, so by now the
+    // predecessors' words are there: no spinning to speak of, only latency -- and that is paid
+    // once per LB_WIDE predecessors (independent loads in flight), not once per predecessor.
+    // Every warp takes part (digit = thread & 255, the two halves of the block redundantly), so
+    // no warp reaches the barrier below much later than the others.
+    {
+        constexpr int LB_WIDE = 4;
+        const unsigned dgt = threadIdx.x & (RADIX - 1);
         uint32_t excl = 0;
-        if (tile > 0) {
-            int64_t t = (int64_t)tile - 1;
-            while (true) {
-                uint32_t st;
-                do { st = ld_relaxed_u32(status + (size_t)t * RADIX + threadIdx.x); } while ((st >> 30) == 0);
-                excl += st & ST_VALUE;
-                if ((st >> 30) == 2) break;
-                t--;
+        int64_t t = (int64_t)tile - 1;
+        bool done = tile == 0;
+        while (!done) {
+            uint32_t st[LB_WIDE];
+#pragma unroll
+            for (int k = 0; k < LB_WIDE; k++)
+                st[k] = t - k >= 0 ? ld_relaxed_u32(status + (size_t)(t - k) * RADIX + dgt) : ST_INCLUSIVE;
+#pragma unroll
+            for (int k = 0; k < LB_WIDE; k++) {
+                if (!done) {
+                    while ((st[k] >> 30) == 0) st[k] = ld_relaxed_u32(status + (size_t)(t - k) * RADIX + dgt);
+                    excl += st[k] & ST_VALUE;
+                    done = (st[k] >> 30) == 2;
+                }
             }
-            st_relaxed_u32(status + (size_t)tile * RADIX + threadIdx.x, ST_INCLUSIVE | (excl + real));
+            t -= LB_WIDE;
         }
-        s_global_off[threadIdx.x] = digit_base[threadIdx.x] + excl - s_digit_start[threadIdx.x];
+        if (threadIdx.x < RADIX) {
+            if (tile > 0) st_relaxed_u32(status + (size_t)tile * RADIX + dgt, ST_INCLUSIVE | (excl + real));
+            s_global_off[dgt] = digit_base[dgt] + excl - s_digit_start[dgt] / KB;
+        }
     }
     __syncthreads();
 
@@ -234,25 +269,40 @@ onesweep_kernel(const K* __restrict__ keys_in, K* __restrict__ keys_out, const u
 #pragma unroll
     for (int j = 0; j < ITEMS; j++) {
         const uint32_t pos = j * SORT_THREADS + threadIdx.x;
-        if (pos < valid) {
+        if (FULL || pos < valid) {
             const K k = s_keys[pos];
             const uint32_t d = (uint32_t)(k >> shift) & mask;
-            keys_out[s_global_off[d] + pos] = k;
+            const uint32_t dst = s_global_off[d] + pos;
+            keys_out[dst] = k;
+            if (HAS_VALUES) vals_out[dst] = s_vals[pos];
         }
     }
-    if (HAS_VALUES) {
-#pragma unroll
-        for (int i = 0; i < ITEMS; i++) s_vals[rank[i]] = val[i];
-        __syncthreads();
-#pragma unroll
-        for (int j = 0; j < ITEMS; j++) {
-            const uint32_t pos = j * SORT_THREADS + threadIdx.x;
-            if (pos < valid) {
-                const uint32_t d = (uint32_t)(s_keys[pos] >> shift) & mask;
-                vals_out[s_global_off[d] + pos] = s_vals[pos];
-            }
-        }
-    }
+}
+
+template <typename K, bool HAS_VALUES>
+__global__ void __launch_bounds__(SORT_THREADS, COL_SORT_CTAS)
+onesweep_kernel(const K* __restrict__ keys_in, K* __restrict__ keys_out, const uint32_t* __restrict__ vals_in,
+                uint32_t* __restrict__ vals_out, uint32_t n, const uint32_t* __restrict__ digit_base,
+                uint32_t* __restrict__ status, unsigned* ticket, uint32_t shift, uint32_t mask, uint32_t bits) {
+    constexpr int ITEMS = Tile<K>::ITEMS;
+    constexpr int TILE = SORT_THREADS * ITEMS;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    __shared__ uint32_t s_digit_start[RADIX];
+    __shared__ uint32_t s_global_off[RADIX];
+    __shared__ uint32_t s_scan_warp[RADIX / 32];
+    __shared__ unsigned s_tile;
+
+    uint32_t* s_whist = reinterpret_cast<uint32_t*>(smem_raw + sizeof(K) * TILE);
+    if (threadIdx.x == 0) s_tile = atomicAdd(ticket, 1u);
+    for (int i = threadIdx.x; i < SORT_WARPS * RADIX; i += SORT_THREADS) s_whist[i] = 0;
+    __syncthreads();
+    const unsigned tile = s_tile;
+    if ((uint64_t)(tile + 1) * TILE <= n)
+        onesweep_tile<K, ITEMS, true, HAS_VALUES>(keys_in, keys_out, vals_in, vals_out, n, digit_base, status, shift,
+                                                  mask, bits, tile, smem_raw, s_digit_start, s_global_off, s_scan_warp);
+    else
+        onesweep_tile<K, ITEMS, false, HAS_VALUES>(keys_in, keys_out, vals_in, vals_out, n, digit_base, status, shift,
+                                                   mask, bits, tile, smem_raw, s_digit_start, s_global_off, s_scan_warp);
 }
 
 template <typename K, bool HAS_VALUES> constexpr size_t onesweep_smem() {
@@ -312,7 +362,6 @@ int run_passes(const K* keys_in, K* keys_out, const uint32_t* vals_in, uint32_t*
         COL_CHECK_LAUNCH();
     }
     const uint32_t mask = (1u << bits) - 1;
-    static const int rank_mode = getenv("COL_SORT_RANK") ? atoi(getenv("COL_SORT_RANK")) : 2;  // tuning aid: 1 = match.any (measured 1.5x slower on B200), 2 = ballot
     for (uint32_t p = 0; p < npass; p++) {
         // the last pass lands in *_out; earlier ones alternate tmp/out backwards from there
         const bool to_out = ((npass - 1 - p) & 1u) == 0;
@@ -321,21 +370,17 @@ int run_passes(const K* keys_in, K* keys_out, const uint32_t* vals_in, uint32_t*
         const uint32_t* vin = p == 0 ? vals_in : (to_out ? tmp_vals : vals_out);
         uint32_t* vout = to_out ? vals_out : tmp_vals;
         uint32_t* status = reinterpret_cast<uint32_t*>(scratch + L.status + L.status_bytes * p);
-#define LAUNCH_ONESWEEP(HV, RK)                                                                              \
-    {                                                                                                        \
-        constexpr size_t smem = onesweep_smem<K, HV>();                                                      \
-        COL_CUDA(cudaFuncSetAttribute(onesweep_kernel<K, HV, RK>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
-                                      (int)smem));                                                           \
-        onesweep_kernel<K, HV, RK><<<(unsigned)L.tiles, SORT_THREADS, smem, s>>>(                            \
-            kin, kout, HV ? vin : nullptr, HV ? vout : nullptr, n, ghist + p * RADIX, status, tickets + p,   \
-            shift0 + p * bits, mask);                                                                        \
-    }
         if (has_vals) {
-            if (rank_mode == 2) LAUNCH_ONESWEEP(true, 2) else LAUNCH_ONESWEEP(true, 1)
+            constexpr size_t smem = onesweep_smem<K, true>();
+            COL_CUDA(cudaFuncSetAttribute(onesweep_kernel<K, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            onesweep_kernel<K, true><<<(unsigned)L.tiles, SORT_THREADS, smem, s>>>(
+                kin, kout, vin, vout, n, ghist + p * RADIX, status, tickets + p, shift0 + p * bits, mask, bits);
         } else {
-            if (rank_mode == 2) LAUNCH_ONESWEEP(false, 2) else LAUNCH_ONESWEEP(false, 1)
+            constexpr size_t smem = onesweep_smem<K, false>();
+            COL_CUDA(cudaFuncSetAttribute(onesweep_kernel<K, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            onesweep_kernel<K, false><<<(unsigned)L.tiles, SORT_THREADS, smem, s>>>(
+                kin, kout, nullptr, nullptr, n, ghist + p * RADIX, status, tickets + p, shift0 + p * bits, mask, bits);
         }
-#undef LAUNCH_ONESWEEP
         COL_CHECK_LAUNCH();
     }
     return 0;
