@@ -159,7 +159,8 @@ class Collider:
         self._total_buf = torch.zeros(1, dtype=torch.int64, device=ctx)
         self._wide_buf = _lib.alloc_bytes(ctx, max(self.size - 1, 1) * 32)   # 32-byte traversal records
         self._scene_buf = _lib.alloc_bytes(ctx, 8 * self.program.coord_dtype.itemsize)   # {min[4], max[4]} of the centres
-        self._trv_scratch = _lib.alloc_bytes(ctx, L.col_traverse_scratch_bytes(self.size))
+        self._trv_scratch = None      # sized by the first call that writes rows (depends on its capacity)
+        self._trv_scratch_bytes = 0
         self._bufs_for = key
 
     def resize(self, size=None, ngroups=None, group_size=None, radix_bits=None):
@@ -237,6 +238,10 @@ class Collider:
         parked), the counts are scanned, the rows are emitted in the deterministic
         order.  Leaves the u64 row count of the range in self._total_buf."""
         L, P, S = _lib.lib(), _lib.ptr, _lib.stream_ptr(cq)
+        need = L.col_traverse_scratch_bytes(q_end - q_begin, n_collisions)
+        if need > self._trv_scratch_bytes:   # (grows with the rows per query: deeper per-query stash)
+            self._trv_scratch = _lib.alloc_bytes(self.program.context, need)
+            self._trv_scratch_bytes = need
         _lib.check(L.col_traverse_wide_pairs(P(collisions_buf), n_collisions, base, P(self._total_buf),
                                              P(self._wide_buf), P(self._bounds_buf), P(self._scene_buf),
                                              P(self._ids_bufs[1]), self.program._code, self.size, q_begin, q_end,

@@ -10,11 +10,11 @@
 //    per diverged lane per load).  Leaves are confirmed on the exact float boxes, so the
 //    reported rows and their order are the reference's, bit for bit.
 //  * count -> scan -> write without a second walk: every query walks once and
-//    parks its first TRV_STASH hits in a k-major global array (coalesced rows, only
+//    parks its first `depth` hits (the stash: 32..128 rows) in a k-major global array (coalesced rows, only
 //    the used ones move); the counts are scanned by the single-pass scan kernel;
 //    an emit kernel copies the parked hits to their final rows.  The row order is
 //    exactly that of the reference's work-items run sequentially (query-major,
-//    DFS order, child a before b).  Only queries with more than TRV_STASH hits walk
+//    DFS order, child a before b).  Only queries with more than `depth` hits walk
 //    a second time, for the remainder.  (A single fused kernel chaining blocks by
 //    decoupled look-back was measured slower: blocks of dense regions stall every
 //    later block, and a shared-memory stash shrinks the L1 the walk depends on.)
@@ -26,7 +26,7 @@
 namespace {
 
 constexpr int TRV_THREADS = 128;
-constexpr int TRV_STASH = 32;
+constexpr uint32_t TRV_STASH_MIN = 32, TRV_STASH_MAX = 128;
 constexpr uint32_t TRV_DONE = 0xFFFFFFFFu;   // stack sentinel / "lane has no node to visit"
 
 struct QNode { uint32_t w[8]; };   // see qnode.cuh
@@ -166,7 +166,7 @@ count_kernel(unsigned long long* __restrict__ total, uint32_t* __restrict__ coun
 
 // ---- walk once: candidates ------------------------------------------------------
 // Every query walks ONCE, on the traversal records only.  The leaves whose grid boxes
-// overlap the query's are CANDIDATES: their number goes to counts[], the first TRV_STASH
+// overlap the query's are CANDIDATES: their number goes to counts[], the first `depth`
 // of them (sorted leaf positions, in reference order) are parked in a k-major global
 // array stash[k * nq + i]: lanes of a warp park their k-th candidate in one 128-byte row,
 // and only rows that are actually used ever move.  No inter-block dependency, so dense
@@ -175,7 +175,7 @@ template <typename T>
 __global__ void __launch_bounds__(TRV_THREADS)
 candidates_kernel(uint32_t* __restrict__ counts, uint32_t* __restrict__ stash, const unsigned char* __restrict__ wide,
                   const T* __restrict__ bounds, const T* __restrict__ scene, uint32_t n, uint32_t q_begin,
-                  uint32_t q_end, uint32_t prefetch_lines) {
+                  uint32_t q_end, uint32_t prefetch_lines, uint32_t depth) {
     const uint32_t nq = q_end - q_begin;
     const uint32_t i = blockIdx.x * TRV_THREADS + threadIdx.x;
     {   // the low levels of the walks of this block live in the records right of its first query
@@ -188,8 +188,8 @@ candidates_kernel(uint32_t* __restrict__ counts, uint32_t* __restrict__ stash, c
     const uint32_t q = q_begin + i, leaf_start = n - 1;
     const Query<T> query = load_query(bounds, leaf_start + q, make_quant(scene));
     uint32_t* park = stash + i;
-    counts[i] = walk<false>(wide, bounds, query, q, leaf_start, [park, nq](uint32_t pos, uint32_t k) {
-        if (k < TRV_STASH) park[(size_t)k * nq] = pos;
+    counts[i] = walk<false>(wide, bounds, query, q, leaf_start, [park, nq, depth](uint32_t pos, uint32_t k) {
+        if (k < depth) park[(size_t)k * nq] = pos;
     });
 }
 
@@ -197,12 +197,12 @@ candidates_kernel(uint32_t* __restrict__ counts, uint32_t* __restrict__ stash, c
 // The exact test of collision.cl:164-166 on the float boxes, batched: thread i runs over
 // its parked candidates (coalesced k-major rows), keeps the confirmed ones in place (same
 // order) and replaces counts[i] by the number of rows of the query.  A query with more
-// than TRV_STASH candidates walks again, exactly, parking its first TRV_STASH rows.
+// than `depth` candidates walks again, exactly, parking its first `depth` rows.
 template <typename T>
 __global__ void __launch_bounds__(TRV_THREADS)
 confirm_kernel(unsigned long long* __restrict__ total, uint32_t* __restrict__ counts, uint32_t* __restrict__ stash,
                const unsigned char* __restrict__ wide, const T* __restrict__ bounds, const T* __restrict__ scene,
-               uint32_t n, uint32_t q_begin, uint32_t q_end) {
+               uint32_t n, uint32_t q_begin, uint32_t q_end, uint32_t depth) {
     const uint32_t nq = q_end - q_begin;
     const uint32_t i = blockIdx.x * TRV_THREADS + threadIdx.x;
     uint32_t hits = 0;
@@ -211,7 +211,7 @@ confirm_kernel(unsigned long long* __restrict__ total, uint32_t* __restrict__ co
         if (cand) {
             const uint32_t q = q_begin + i, leaf_start = n - 1;
             uint32_t* park = stash + i;
-            if (cand <= TRV_STASH) {
+            if (cand <= depth) {
                 const LeafBox<T> b = load_leaf_box(bounds, leaf_start + q);
                 Query<T> query;
 #pragma unroll
@@ -225,8 +225,8 @@ confirm_kernel(unsigned long long* __restrict__ total, uint32_t* __restrict__ co
                 }
             } else {
                 const Query<T> query = load_query(bounds, leaf_start + q, make_quant(scene));
-                hits = walk<true>(wide, bounds, query, q, leaf_start, [park, nq](uint32_t pos, uint32_t k) {
-                    if (k < TRV_STASH) park[(size_t)k * nq] = pos;
+                hits = walk<true>(wide, bounds, query, q, leaf_start, [park, nq, depth](uint32_t pos, uint32_t k) {
+                    if (k < depth) park[(size_t)k * nq] = pos;
                 });
             }
             counts[i] = hits;
@@ -238,14 +238,14 @@ confirm_kernel(unsigned long long* __restrict__ total, uint32_t* __restrict__ co
 // ---- emit: rows to their final, deterministic positions -----------------------
 // offsets = exclusive scan of counts.  Row k of query i lands at base + offsets[i] + k
 // (query-major, DFS order: the order of the reference's work-items run sequentially).
-// Parked hits are simply copied (ids gathered); a query with more than TRV_STASH hits
+// Parked hits are simply copied (ids gathered); a query with more than `depth` hits
 // walks again for the remainder only.
 template <typename T>
 __global__ void __launch_bounds__(TRV_THREADS)
 emit_kernel(uint32_t* __restrict__ pairs, uint64_t capacity, uint64_t base, const uint32_t* __restrict__ offsets,
             const unsigned long long* __restrict__ total, const uint32_t* __restrict__ stash,
             const unsigned char* __restrict__ wide, const T* __restrict__ bounds, const T* __restrict__ scene,
-            const uint32_t* __restrict__ ids, uint32_t n, uint32_t q_begin, uint32_t q_end) {
+            const uint32_t* __restrict__ ids, uint32_t n, uint32_t q_begin, uint32_t q_end, uint32_t depth) {
     const uint32_t i = blockIdx.x * TRV_THREADS + threadIdx.x;
     const uint32_t q = q_begin + i;
     if (q >= q_end) return;
@@ -256,18 +256,18 @@ emit_kernel(uint32_t* __restrict__ pairs, uint64_t capacity, uint64_t base, cons
     const uint64_t out = base + off;
     if (hits == 0 || out >= capacity) return;
     const uint32_t qid = __ldg(ids + q);
-    const uint32_t parked = min(hits, (uint32_t)TRV_STASH);
+    const uint32_t parked = min(hits, depth);
     for (uint32_t k = 0; k < parked; k++) {
         const uint64_t at = out + k;
         if (at < capacity)
             *reinterpret_cast<uint2*>(pairs + at * 2) = make_uint2(qid, __ldg(ids + __ldg(stash + (size_t)k * nq + i)));
     }
-    if (hits > TRV_STASH) {
+    if (hits > depth) {
         const uint32_t leaf_start = n - 1;
         const Query<T> query = load_query(bounds, leaf_start + q, make_quant(scene));
         walk<true>(wide, bounds, query, q, leaf_start, [=](uint32_t pos, uint32_t k) {
             const uint64_t at = out + k;
-            if (k >= TRV_STASH && at < capacity)
+            if (k >= depth && at < capacity)
                 *reinterpret_cast<uint2*>(pairs + at * 2) = make_uint2(qid, __ldg(ids + pos));
         });
     }
@@ -296,19 +296,30 @@ inline bool bad_range(uint32_t n, uint32_t q_begin, uint32_t q_end) { return q_e
 
 }  // namespace
 
-// scratch of col_traverse_wide_pairs: [counts/offsets: nq u32][scan scratch][stash: TRV_STASH x nq u32]
+// Depth of the per-query stash: deep enough that few queries overflow it (an overflowing
+// query walks two more times).  Chosen from the rows per query the caller made room for
+// (normally the result of a count-only call); the same rule sizes the scratch.
+static uint32_t stash_depth(uint32_t nq, uint64_t capacity) {
+    const uint64_t per_query = capacity / (nq ? nq : 1);
+    return per_query <= 6 ? TRV_STASH_MIN : per_query <= 24 ? 64u : TRV_STASH_MAX;
+}
+
+// scratch of col_traverse_wide_pairs: [counts/offsets: nq u32][scan scratch][stash: depth x nq u32]
 struct PairsLayout { size_t counts, scan, stash, total; };
-static PairsLayout pairs_layout(uint32_t nq) {
+static PairsLayout pairs_layout(uint32_t nq, uint32_t depth) {
     auto up = [](size_t x) { return (x + 255) & ~(size_t)255; };
     PairsLayout L;
     L.counts = 0;
     L.scan = up((size_t)nq * 4 + 4);
     L.stash = L.scan + up(col_scan_scratch_bytes(nq));
-    L.total = L.stash + up((size_t)nq * 4 * TRV_STASH);
+    L.total = L.stash + up((size_t)nq * 4 * depth);
     return L;
 }
 
-COL_API size_t col_traverse_scratch_bytes(uint32_t n_queries) { return pairs_layout(n_queries ? n_queries : 1).total; }
+COL_API size_t col_traverse_scratch_bytes(uint32_t n_queries, uint64_t capacity) {
+    const uint32_t nq = n_queries ? n_queries : 1;
+    return pairs_layout(nq, stash_depth(nq, capacity)).total;
+}
 
 COL_API int col_traverse_wide_count(uint64_t* total, uint32_t* counts, const void* wide, const void* bounds,
                                     const void* scene2x4, int dtype, uint32_t n, uint32_t q_begin, uint32_t q_end,
@@ -335,18 +346,19 @@ static int pairs_impl(uint32_t* pairs, uint64_t capacity, uint64_t base, unsigne
                       uint32_t q_begin, uint32_t q_end, char* sc, void* stream) {
     cudaStream_t s = col_stream(stream);
     const uint32_t nq = q_end - q_begin;
-    const PairsLayout L = pairs_layout(nq);
+    const uint32_t depth = stash_depth(nq, capacity);
+    const PairsLayout L = pairs_layout(nq, depth);
     uint32_t* counts = reinterpret_cast<uint32_t*>(sc + L.counts);
     uint32_t* stash = reinterpret_cast<uint32_t*>(sc + L.stash);
     const unsigned blocks = col_blocks(nq, TRV_THREADS);
     static const uint32_t pf = getenv("COL_TRV_PF") ? atoi(getenv("COL_TRV_PF")) : 64;
-    candidates_kernel<T><<<blocks, TRV_THREADS, 0, s>>>(counts, stash, w, bounds, scene, n, q_begin, q_end, pf);
+    candidates_kernel<T><<<blocks, TRV_THREADS, 0, s>>>(counts, stash, w, bounds, scene, n, q_begin, q_end, pf, depth);
     COL_CHECK_LAUNCH();
-    confirm_kernel<T><<<blocks, TRV_THREADS, 0, s>>>(total, counts, stash, w, bounds, scene, n, q_begin, q_end);
+    confirm_kernel<T><<<blocks, TRV_THREADS, 0, s>>>(total, counts, stash, w, bounds, scene, n, q_begin, q_end, depth);
     COL_CHECK_LAUNCH();
     const int rc = col_exclusive_scan_u32(counts, nq, nullptr, sc + L.scan, stream);
     if (rc) return rc;
-    emit_kernel<T><<<blocks, TRV_THREADS, 0, s>>>(pairs, capacity, base, counts, total, stash, w, bounds, scene, ids, n, q_begin, q_end);
+    emit_kernel<T><<<blocks, TRV_THREADS, 0, s>>>(pairs, capacity, base, counts, total, stash, w, bounds, scene, ids, n, q_begin, q_end, depth);
     COL_CHECK_LAUNCH();
     return 0;
 }

@@ -180,13 +180,15 @@ int col_traverse_atomic(uint32_t* pairs, uint32_t* counter, uint32_t capacity, c
  * lands at base + (number of rows of queries q_begin..q-1) + k when that index
  * is < capacity; *total_out (u64, required) = rows found in the range (the list
  * positions are exact for totals < 2^32 per call).  capacity == 0: count only.
- * scratch: col_traverse_scratch_bytes(q_end - q_begin).
+ * scratch: col_traverse_scratch_bytes(q_end - q_begin, capacity) -- the per-query stash is
+ * 32, 64 or 128 rows deep depending on the rows per query the caller made room for; a
+ * scratch sized for a capacity serves every call with that capacity or less.
  * ids_sorted: ids in sorted order (the sort's payload output). */
 int col_build_tree_wide(const uint32_t* codes_sorted, const uint32_t* ids_sorted, void* nodes, void* wide,
                         uint32_t* flags, uint32_t n, void* stream);
 int col_refit_wide(void* bounds, void* wide, uint32_t* flags, const void* nodes, const void* coords4,
                    const void* radii, const void* scene2x4, int dtype, uint32_t n, void* stream);
-size_t col_traverse_scratch_bytes(uint32_t n_queries);
+size_t col_traverse_scratch_bytes(uint32_t n_queries, uint64_t capacity);
 int col_traverse_wide_count(uint64_t* total, uint32_t* counts, const void* wide, const void* bounds,
                             const void* scene2x4, int dtype, uint32_t n, uint32_t q_begin, uint32_t q_end,
                             void* stream);

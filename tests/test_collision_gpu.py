@@ -299,7 +299,7 @@ def test_wide_count_and_write_entry_points(cuda_env, oracle):
         rows.append(to_host(out, 'uint32', (int(cnt.sum()), 2)))
         # fused over the same sub-range gives the same rows
         out2 = dev_empty(max(int(cnt.sum()), 1) * 8)
-        scr = dev_empty(L.col_traverse_scratch_bytes(qe - qb))
+        scr = dev_empty(L.col_traverse_scratch_bytes(qe - qb, int(cnt.sum())))
         assert L.col_traverse_wide_pairs(P(out2), int(cnt.sum()), 0, P(tot), P(col._wide_buf), P(col._bounds_buf),
                                          P(col._scene_buf), P(col._ids_bufs[1]), 0, n, qb, qe, P(scr), S) == 0
         cq.synchronize()

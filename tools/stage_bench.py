@@ -112,6 +112,7 @@ def main():
     m = int(col._total_buf.item())
     print("pairs M = {} ({:.2f} per sphere)".format(m, m / n))
     pairs = torch.empty(max(m, 1) * 2, dtype=torch.int32, device=dev)
+    scr_ = _lib.alloc_bytes(dev, L.col_traverse_scratch_bytes(n, m))
     report("traverse write", T(lambda: L.col_traverse_write(P(pairs), m, P(col._counts_buf), 0, P(col._nodes_buf), P(col._bounds_buf), code, n, 0, n, S)), 36 * n + 8 * m)
     report("traverse atomic (count only)", T(lambda: L.col_traverse_atomic(None, P(n_buf), 0, P(col._nodes_buf), P(col._bounds_buf), code, n, 0, n, S)), 36 * n)
 
@@ -121,7 +122,7 @@ def main():
     report("leaf boxes + refit (wide)", T(lambda: L.col_refit_wide(P(col._bounds_buf), P(col._wide_buf), P(col._flags_buf), P(col._nodes_buf), P(coords), P(radii), P(col._scene_buf), code, n, S),
                                           setup=lambda: L.col_build_tree_wide(P(col._codes_bufs[1]), P(col._ids_bufs[1]), P(col._nodes_buf), P(col._wide_buf), P(col._flags_buf), n, S)), 192 * n)
     report("traverse wide count", T(lambda: L.col_traverse_wide_count(P(col._total_buf), None, P(col._wide_buf), P(col._bounds_buf), P(col._scene_buf), code, n, 0, n, S)), 36 * n)
-    report("traverse wide pairs (walk+scan+emit)", T(lambda: L.col_traverse_wide_pairs(P(pairs), m, 0, P(col._total_buf), P(col._wide_buf), P(col._bounds_buf), P(col._scene_buf), P(col._ids_bufs[1]), code, n, 0, n, P(col._trv_scratch), S)), 36 * n + 8 * m)
+    report("traverse wide pairs (walk+scan+emit)", T(lambda: L.col_traverse_wide_pairs(P(pairs), m, 0, P(col._total_buf), P(col._wide_buf), P(col._bounds_buf), P(col._scene_buf), P(col._ids_bufs[1]), code, n, 0, n, P(scr_), S)), 36 * n + 8 * m)
     torch.cuda.synchronize()
     assert int(col._total_buf.item()) == m, (int(col._total_buf.item()), m)
 

@@ -25,11 +25,12 @@ n_buf = torch.zeros(1, dtype=torch.int32, device=dev)
 col.get_collisions(cq, coords, radii, n_buf, None, 0).synchronize()
 m = int(n_buf.item()) & 0xFFFFFFFF
 pairs = torch.empty(max(m, 1) * 2, dtype=torch.int32, device=dev)
+scr_ = _lib.alloc_bytes(dev, L.col_traverse_scratch_bytes(n, m))
 T = Timer(dev, args.reps)
 if args.no_flush:
     T.flush = torch.empty(16, dtype=torch.uint8, device=dev)
 code = 0
 t1 = T(lambda: L.col_traverse_wide_count(P(col._total_buf), None, P(col._wide_buf), P(col._bounds_buf), P(col._scene_buf), code, n, 0, n, S))
-t2 = T(lambda: L.col_traverse_wide_pairs(P(pairs), m, 0, P(col._total_buf), P(col._wide_buf), P(col._bounds_buf), P(col._scene_buf), P(col._ids_bufs[1]), code, n, 0, n, P(col._trv_scratch), S))
+t2 = T(lambda: L.col_traverse_wide_pairs(P(pairs), m, 0, P(col._total_buf), P(col._wide_buf), P(col._bounds_buf), P(col._scene_buf), P(col._ids_bufs[1]), code, n, 0, n, P(scr_), S))
 t3 = T(lambda: col.get_collisions(cq, coords, radii, n_buf, pairs, m))
 print("n={} m={} count {:.3f} ms  pairs {:.3f} ms  full {:.3f} ms".format(n, m, t1, t2, t3))
