@@ -213,7 +213,7 @@ def run_ours(args):
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
 
     if world == 1:
-        collider = Collider(dev, n, 8, 128)
+        collider = Collider(dev, n, 8, 128, graph=not args.no_graph)
     else:
         from collision_b200.sharded import ShardedCollider
         collider = ShardedCollider(dev, n, 8, 128, mode=args.multi_gpu_mode)
@@ -257,7 +257,6 @@ def run_ours(args):
     barrier()
 
     # ---- device-resident timing: K steps, one event pair per step, L2 flushed in between
-    collider.stage_events = []
     launches0 = collider.kernel_launches
     step_events = []
     barrier()
@@ -275,6 +274,16 @@ def run_ours(args):
     step_ms = [a.elapsed_time(b) for a, b in step_events]
     total_ms = float(sum(step_ms))
     launches = collider.kernel_launches - launches0
+
+    # ---- per-stage times (roofline of the dominant kernel): a few more steps with event marks
+    # between the stages (marks switch the CUDA-graph replay off, so these steps are not the timed ones)
+    collider.stage_events = []
+    for _ in range(max(5, args.steps // 2)):
+        flush.fill_(0)
+        cq.wait_stream(torch.cuda.current_stream())
+        step()
+        torch.cuda.current_stream().wait_stream(cq)
+    barrier()
     marks = collider.stage_events
     collider.stage_events = None
     stage_ms = {}
@@ -389,7 +398,8 @@ def run_ours(args):
             "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic",
-            "config": workload_config(n, {"parallelism": "single GPU" if world == 1 else
+            "config": workload_config(n, {"launch": "CUDA graph replay" if (world == 1 and not args.no_graph) else "kernel by kernel",
+                                          "parallelism": "single GPU" if world == 1 else
                                           "{}: traversal sharded over {} contiguous Morton ranges, NCCL "
                                           "broadcast + all_gather of row totals".format(args.multi_gpu_mode, world)}),
             "pairs": total, "pairs_per_sec": total / (ms_per_step * 1e-3),
@@ -415,6 +425,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
+    ap.add_argument("--no-graph", action="store_true", help="enqueue kernel by kernel instead of replaying a CUDA graph")
     ap.add_argument("--multi-gpu-mode", choices=["broadcast_tree", "replicate_build"], default="replicate_build",
                     help="N>1: broadcast the tree built on rank 0 (north_star) or the inputs and build everywhere")
     args = ap.parse_args()

@@ -108,7 +108,7 @@ class Collider:
 
     def __init__(self, ctx, size, ngroups, group_size, coord_dtype=dtype('float32'),
                  program=None, sorter_programs=(None, None), reducer_program=None, ordered=True,
-                 layout="wide"):
+                 layout="wide", graph=False):
         coord_dtype = dtype(coord_dtype)
         self.size = size
         self.group_size = group_size
@@ -139,6 +139,13 @@ class Collider:
         # kernel_launches counts the kernels this object has enqueued
         self.stage_events = None
         self.kernel_launches = 0
+        # graph=True: the launch sequence of get_collisions is captured into a CUDA graph the
+        # second time it is called with the same buffers, sizes and stream, and replayed from
+        # then on (one graph launch instead of ~17 enqueues: the short kernels at the head of
+        # the pipeline are otherwise bound by the host's enqueue rate)
+        self.graph = bool(graph)
+        self._graphs = {}
+        self._graph_candidate = None
 
     # -- scratch ----------------------------------------------------------
     def _ensure_scratch(self):
@@ -147,6 +154,8 @@ class Collider:
             return
         ctx = self.program.context
         L = _lib.lib()
+        self._graphs.clear()          # captured graphs point into the scratch being replaced
+        self._graph_candidate = None
         # can't sort in place (collision.py:60-69)
         self._ids_bufs = [_lib.alloc_bytes(ctx, self.padded_size * 4) for _ in range(2)]
         self._codes_bufs = [_lib.alloc_bytes(ctx, self.padded_size * 4) for _ in range(2)]
@@ -188,13 +197,36 @@ class Collider:
             raise ValueError("Invalid collisions_buf for n_collisions > 0")
         self._ensure_scratch()
         _lib.begin(cq, wait_for)
+        if self.graph and self.stage_events is None:
+            key = (cq.cuda_stream, self.size, n_collisions, _lib.ptr(coords_buf), _lib.ptr(radii_buf),
+                   _lib.ptr(n_collisions_buf), _lib.ptr(collisions_buf))
+            entry = self._graphs.get(key)
+            if entry is None and self._graph_candidate == key:
+                # second call with this signature: scratch is allocated, capture the sequence
+                g = torch.cuda.CUDAGraph()
+                before = self.kernel_launches
+                with torch.cuda.graph(g, stream=cq):
+                    self._enqueue(cq, coords_buf, radii_buf, n_collisions_buf, collisions_buf, n_collisions)
+                entry = self._graphs[key] = (g, self.kernel_launches - before)
+                self.kernel_launches = before
+                # (buffers named in the key are referenced by the graph: the caller keeps them alive,
+                #  as it must for any enqueued work)
+            if entry is not None:
+                with torch.cuda.stream(cq):
+                    entry[0].replay()
+                self.kernel_launches += entry[1]
+                return _lib.done(cq)
+            self._graph_candidate = key
+        self._enqueue(cq, coords_buf, radii_buf, n_collisions_buf, collisions_buf, n_collisions)
+        return _lib.done(cq)
+
+    def _enqueue(self, cq, coords_buf, radii_buf, n_collisions_buf, collisions_buf, n_collisions):
         self._mark(cq, "begin", 0)
         self._sort_stage(cq, coords_buf)
         if self.fast:
             self._traverse_fast(cq, coords_buf, radii_buf, n_collisions_buf, collisions_buf, n_collisions)
         else:
             self._traverse_reference_layout(cq, coords_buf, radii_buf, n_collisions_buf, collisions_buf, n_collisions)
-        return _lib.done(cq)
 
     def _mark(self, cq, name, kernels):
         self.kernel_launches += kernels
@@ -242,6 +274,8 @@ class Collider:
         if need > self._trv_scratch_bytes:   # (grows with the rows per query: deeper per-query stash)
             self._trv_scratch = _lib.alloc_bytes(self.program.context, need)
             self._trv_scratch_bytes = need
+            self._graphs.clear()
+            self._graph_candidate = None
         _lib.check(L.col_traverse_wide_pairs(P(collisions_buf), n_collisions, base, P(self._total_buf),
                                              P(self._wide_buf), P(self._bounds_buf), P(self._scene_buf),
                                              P(self._ids_bufs[1]), self.program._code, self.size, q_begin, q_end,

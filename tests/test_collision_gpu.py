@@ -306,3 +306,38 @@ def test_wide_count_and_write_entry_points(cuda_env, oracle):
         np.testing.assert_equal(to_host(out2, 'uint32', (int(cnt.sum()), 2)), rows[-1])
         assert int(tot.item()) == int(cnt.sum())
     np.testing.assert_equal(np.concatenate(rows), want['pairs'])
+
+
+def test_graph_replay_matches_plain_enqueue(cuda_env, oracle):
+    """Collider(graph=True): the captured launch sequence replays to the same rows, for
+    changing inputs in the same buffers, and is re-captured when the capacity changes."""
+    import numpy as np
+    import torch
+    from collision_b200.collision import Collider
+    dev, cq = cuda_env
+    n = 5000
+    col = Collider(dev, n, 8, 128, graph=True)
+    n_buf = torch.zeros(1, dtype=torch.int32, device=dev)
+    coords_d = torch.zeros(n, 4, dtype=torch.float32, device=dev)
+    radii_d = torch.zeros(n, dtype=torch.float32, device=dev)
+    cap = 60000
+    pairs_d = torch.zeros(cap * 2, dtype=torch.int32, device=dev)
+    for seed in range(5):
+        rs = np.random.RandomState(seed)
+        coords = np.zeros((n, 4), np.float32)
+        coords[:, :3] = rs.random_sample((n, 3))
+        radii = np.full(n, 0.02 + 0.002 * seed, np.float32)
+        want = oracle.collide(coords, radii)
+        coords_d.copy_(torch.from_numpy(coords))
+        radii_d.copy_(torch.from_numpy(radii))
+        torch.cuda.synchronize()
+        col.get_collisions(cq, coords_d, radii_d, n_buf, pairs_d, cap).synchronize()
+        total = int(n_buf.item()) & 0xFFFFFFFF
+        assert total == want["total"] and total <= cap
+        got = pairs_d.cpu().numpy().view(np.uint32).reshape(-1, 2)[:total]
+        assert np.array_equal(got, want["pairs"])
+    assert len(col._graphs) == 1
+    # a different capacity is a different launch sequence
+    col.get_collisions(cq, coords_d, radii_d, n_buf, pairs_d, cap // 2).synchronize()
+    col.get_collisions(cq, coords_d, radii_d, n_buf, pairs_d, cap // 2).synchronize()
+    assert (int(n_buf.item()) & 0xFFFFFFFF) == want["total"]
