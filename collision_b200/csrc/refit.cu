@@ -49,6 +49,23 @@ __device__ __forceinline__ float vmax(float a, float b) { return fmaxf(a, b); }
 __device__ __forceinline__ double vmin(double a, double b) { return fmin(a, b); }
 __device__ __forceinline__ double vmax(double a, double b) { return fmax(a, b); }
 
+// one arrival on a node's counter with release + acquire semantics at GPU scope (cheaper than
+// the two sequentially-consistent __threadfence() around a relaxed atomic it replaces)
+__device__ __forceinline__ uint32_t arrive_acq_rel(uint32_t* p) {
+    uint32_t old;
+    asm volatile("atom.add.acq_rel.gpu.global.u32 %0, [%1], 1;" : "=r"(old) : "l"(p) : "memory");
+    return old;
+}
+
+__device__ __forceinline__ uint32_t arrive_acq_rel_shared(unsigned* p) {
+    uint32_t old;
+    asm volatile("atom.add.acq_rel.cta.shared.u32 %0, [%1], 1;"
+                 : "=r"(old)
+                 : "r"((uint32_t)__cvta_generic_to_shared(p))
+                 : "memory");
+    return old;
+}
+
 template <typename T>
 __device__ __forceinline__ Box<T> leaf_box(const T* __restrict__ coords, const T* __restrict__ radii, uint32_t id) {
     Box<T> b;
@@ -92,9 +109,8 @@ refit_kernel(T* __restrict__ bounds, uint32_t* __restrict__ flags, const col_nod
     if (n < 2) return;
     while (true) {
         const uint32_t parent = rec.x;
-        __threadfence();  // my child's box is visible before my arrival is
-        if (atomicAdd(flags + parent, 1u) < 1u) return;  // first to arrive: the sibling will carry on
-        __threadfence();
+        // my child's box is visible before my arrival is (release), the sibling's after it (acquire)
+        if (arrive_acq_rel(flags + parent) < 1u) return;  // first to arrive: the sibling will carry on
         rec = __ldg(reinterpret_cast<const uint4*>(nodes + parent));  // {grandparent, right_edge, child a, child b}
         const uint32_t sibling = rec.z == node ? rec.w : rec.z;
         const Box<T> other = load_box_cg(bounds, sibling);
@@ -149,9 +165,7 @@ refit_wide_kernel(T* __restrict__ bounds, unsigned char* __restrict__ wide, uint
                 s_box[slot][half][k] = box.lo[k];
                 s_box[slot][half][3 + k] = box.hi[k];
             }
-            __threadfence_block();
-            if (atomicAdd(&s_cnt[slot], 1u) == 0u) return;  // first to arrive: the sibling carries on
-            __threadfence_block();
+            if (arrive_acq_rel_shared(&s_cnt[slot]) == 0u) return;  // first to arrive: the sibling carries on
 #pragma unroll
             for (int k = 0; k < 3; k++) {
                 other.lo[k] = s_box[slot][half ^ 1][k];
@@ -159,9 +173,8 @@ refit_wide_kernel(T* __restrict__ bounds, unsigned char* __restrict__ wide, uint
             }
         } else {
             // my exact box is already in the Bound array (stored below / at the leaf)
-            __threadfence();  // ... and visible before my arrival is
-            if (atomicAdd(flags + parent, 1u) < 1u) return;
-            __threadfence();
+            // ... and visible before my arrival is (release); the sibling's box after it (acquire)
+            if (arrive_acq_rel(flags + parent) < 1u) return;
             other = load_box_cg(bounds, half == 0 ? rec.w : rec.z);
         }
         {   // the node's traversal record: both children, quantised outward
