@@ -25,7 +25,10 @@
 
 namespace {
 
-constexpr int TRV_THREADS = 128;
+#ifndef COL_TRV_THREADS
+#define COL_TRV_THREADS 256
+#endif
+constexpr int TRV_THREADS = COL_TRV_THREADS;
 constexpr uint32_t TRV_STASH_MIN = 32, TRV_STASH_MAX = 128;
 constexpr uint32_t TRV_DONE = 0xFFFFFFFFu;   // stack sentinel / "lane has no node to visit"
 
