@@ -1,7 +1,8 @@
 // qnode.cuh -- the 32-byte traversal record and its conservative quantisation.
 //
 // One record per internal node (written by tree.cu + refit.cu, read by traverse_wide.cu):
-//   w0 = child a, w1 = child b,
+//   w0 = child a, w1 = child b: an internal node as its index, a leaf as 0x80000000 | its sorted
+//        position (so "is it a leaf", "its right edge" and "what to report" need no n),
 //   w2..w4 = box of child a, w5..w7 = box of child b, each as 6 x u16
 //             {lo.x lo.y | lo.z ~hi.x | ~hi.y ~hi.z}          (~v = 65535 - v)
 // A visit is ONE 256-bit load.  The query carries {hi.x hi.y | hi.z ~lo.x | ~lo.y ~lo.z}, so the
@@ -16,8 +17,8 @@
 // order are identical to the reference walk's.
 //
 // Right edges need no storage: child a of node X is a left child, so in Karras numbering
-// its index IS its right edge (internal) or index - (n-1) (leaf); child b's right edge is
-// X's own, which was already checked (> q) when X was entered.
+// its index IS its right edge (internal), as is its position (leaf): w0 & 0x7fffffff either
+// way; child b's right edge is X's own, which was already checked (> q) when X was entered.
 #pragma once
 #include "common.cuh"
 

@@ -103,17 +103,22 @@ __device__ __forceinline__ uint32_t visit(const unsigned char* __restrict__ wide
                                           uint32_t* stack, int& sp, F&& on_leaf) {
     const QNode w = load_qnode(wide, idx);
     const uint32_t ca = w.w[0], cb = w.w[1];
-    const bool la = ca >= leaf_start, lb = cb >= leaf_start;
+    const bool la = (int32_t)ca < 0, lb = (int32_t)cb < 0;   // leaf: 0x80000000 | sorted position
+    const uint32_t pa = ca & 0x7fffffffu, pb = cb & 0x7fffffffu;
     // child a is a left child: its right edge is its own index (leaf: its position);
     // child b's right edge is this node's, already known to be > q
-    const uint32_t ra = la ? ca - leaf_start : ca;
-    const bool oa = grid_overlap(query.grid, w.w[2], w.w[3], w.w[4]) && ra > q;
+    const bool oa = grid_overlap(query.grid, w.w[2], w.w[3], w.w[4]) && pa > q;
     const bool ob = grid_overlap(query.grid, w.w[5], w.w[6], w.w[7]);
-    if (oa && la) {
-        if (!EXACT || exact_overlap(query, load_leaf_box(bounds, ca))) on_leaf(ca - leaf_start);
-    }
-    if (ob && lb) {
-        if (!EXACT || exact_overlap(query, load_leaf_box(bounds, cb))) on_leaf(cb - leaf_start);
+    if (EXACT) {
+        if (oa && la) {
+            if (exact_overlap(query, load_leaf_box(bounds, leaf_start + pa))) on_leaf(pa, true);
+        }
+        if (ob && lb) {
+            if (exact_overlap(query, load_leaf_box(bounds, leaf_start + pb))) on_leaf(pb, true);
+        }
+    } else {   // straight-line: the reports are predicated, not branched around
+        on_leaf(pa, oa && la);
+        on_leaf(pb, ob && lb);
     }
     const bool ta = oa && !la, tb = ob && !lb;
     if (!ta && !tb) return stack[--sp];
@@ -132,7 +137,10 @@ __device__ __forceinline__ uint32_t walk(const unsigned char* __restrict__ wide,
     stack[sp++] = TRV_DONE;
     uint32_t idx = 0, hits = 0;
     do {
-        idx = visit<EXACT>(wide, bounds, query, q, leaf_start, idx, stack, sp, [&](uint32_t pos) { on_leaf(pos, hits); hits++; });
+        idx = visit<EXACT>(wide, bounds, query, q, leaf_start, idx, stack, sp, [&](uint32_t pos, bool valid) {
+            on_leaf(pos, hits, valid);
+            hits += valid ? 1u : 0u;
+        });
     } while (idx != TRV_DONE);
     return hits;
 }
@@ -161,7 +169,7 @@ count_kernel(unsigned long long* __restrict__ total, uint32_t* __restrict__ coun
     if (q < q_end) {
         const uint32_t leaf_start = n - 1;
         const Query<T> query = load_query(bounds, leaf_start + q, make_quant(scene));
-        hits = walk<true>(wide, bounds, query, q, leaf_start, [](uint32_t, uint32_t) {});
+        hits = walk<true>(wide, bounds, query, q, leaf_start, [](uint32_t, uint32_t, bool) {});
         if (counts) counts[q - q_begin] = hits;
     }
     block_add(total, hits);
@@ -191,8 +199,8 @@ candidates_kernel(uint32_t* __restrict__ counts, uint32_t* __restrict__ stash, c
     const uint32_t q = q_begin + i, leaf_start = n - 1;
     const Query<T> query = load_query(bounds, leaf_start + q, make_quant(scene));
     uint32_t* park = stash + i;
-    counts[i] = walk<false>(wide, bounds, query, q, leaf_start, [park, nq, depth](uint32_t pos, uint32_t k) {
-        if (k < depth) park[(size_t)k * nq] = pos;
+    counts[i] = walk<false>(wide, bounds, query, q, leaf_start, [park, nq, depth](uint32_t pos, uint32_t k, bool valid) {
+        if (valid && k < depth) park[(size_t)k * nq] = pos;
     });
 }
 
@@ -228,7 +236,7 @@ confirm_kernel(unsigned long long* __restrict__ total, uint32_t* __restrict__ co
                 }
             } else {
                 const Query<T> query = load_query(bounds, leaf_start + q, make_quant(scene));
-                hits = walk<true>(wide, bounds, query, q, leaf_start, [park, nq, depth](uint32_t pos, uint32_t k) {
+                hits = walk<true>(wide, bounds, query, q, leaf_start, [park, nq, depth](uint32_t pos, uint32_t k, bool) {
                     if (k < depth) park[(size_t)k * nq] = pos;
                 });
             }
@@ -268,7 +276,7 @@ emit_kernel(uint32_t* __restrict__ pairs, uint64_t capacity, uint64_t base, cons
     if (hits > depth) {
         const uint32_t leaf_start = n - 1;
         const Query<T> query = load_query(bounds, leaf_start + q, make_quant(scene));
-        walk<true>(wide, bounds, query, q, leaf_start, [=](uint32_t pos, uint32_t k) {
+        walk<true>(wide, bounds, query, q, leaf_start, [=](uint32_t pos, uint32_t k, bool) {
             const uint64_t at = out + k;
             if (k >= depth && at < capacity)
                 *reinterpret_cast<uint2*>(pairs + at * 2) = make_uint2(qid, __ldg(ids + pos));
@@ -289,7 +297,7 @@ write_kernel(uint32_t* __restrict__ pairs, uint64_t capacity, const uint32_t* __
     if (out >= capacity) return;
     const Query<T> query = load_query(bounds, leaf_start + q, make_quant(scene));
     const uint32_t qid = __ldg(ids + q);
-    walk<true>(wide, bounds, query, q, leaf_start, [=](uint32_t pos, uint32_t k) {
+    walk<true>(wide, bounds, query, q, leaf_start, [=](uint32_t pos, uint32_t k, bool) {
         const uint64_t at = out + k;
         if (at < capacity) *reinterpret_cast<uint2*>(pairs + at * 2) = make_uint2(qid, __ldg(ids + pos));
     });

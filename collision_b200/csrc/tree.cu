@@ -78,7 +78,9 @@ build_tree_kernel(const uint32_t* __restrict__ codes, const uint32_t* __restrict
     nodes[child_a].parent = i;
     nodes[child_b].parent = i;
     if (WIDE) {
-        *reinterpret_cast<uint2*>(wide + (size_t)i * 32) = make_uint2(child_a, child_b);
+        // children in the record: a leaf as 0x80000000 | its sorted position, an internal node as its index
+        *reinterpret_cast<uint2*>(wide + (size_t)i * 32) =
+            make_uint2(lo == gamma ? (0x80000000u | gamma) : gamma, hi == gamma + 1 ? (0x80000000u | (gamma + 1)) : gamma + 1);
         // arrival word of the refit (refit.cu): marked when all leaves of the node lie in one
         // 256-leaf window, i.e. inside one refit block, which then resolves it in shared memory
         flags[i] = ((lo >> 8) == (hi >> 8)) ? 0x80000000u : 0u;
