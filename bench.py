@@ -306,8 +306,9 @@ def run_ours(args):
         torch.cuda.synchronize()
         t0 = time.perf_counter()
         with torch.cuda.stream(cq):
-            coords_d.copy_(coords_pin, non_blocking=True)
-            radii_d.copy_(radii_pin, non_blocking=True)
+            if rank == 0:   # the scene lives in rank 0's host memory; the other ranks receive it over NVLink
+                coords_d.copy_(coords_pin, non_blocking=True)
+                radii_d.copy_(radii_pin, non_blocking=True)
             collider.get_collisions(cq, coords_d, radii_d, n_buf, pairs_d, local_cap, **kw)
             n_pin.copy_(n_buf, non_blocking=True)
         cq.synchronize()
@@ -340,8 +341,9 @@ def run_ours(args):
             with torch.cuda.stream(up):
                 if computed[b] is not None:
                     up.wait_event(computed[b])          # inputs of step i-2 no longer needed
-                coords_db[b].copy_(coords_pin, non_blocking=True)
-                radii_db[b].copy_(radii_pin, non_blocking=True)
+                if rank == 0:
+                    coords_db[b].copy_(coords_pin, non_blocking=True)
+                    radii_db[b].copy_(radii_pin, non_blocking=True)
                 uploaded = torch.cuda.Event()
                 uploaded.record(up)
             if downloaded[b] is not None:
