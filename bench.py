@@ -171,7 +171,8 @@ def run_reference(args):
 # dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu --set full
 # capture of this workload (profiles/r1c_ncu_full_summary.txt; cold cache under ncu):
 # candidates 112.4 + confirm 78.9 + scan 8.4 + emit 49.4 MB
-NCU_TRAFFIC = {"traverse_pairs": 249.1e6, "refit": 152.7e6, "tree": 57.1e6, "bounds": 16.8e6, "morton": 25.2e6}
+NCU_TRAFFIC = {"traverse_pairs": 249.1e6, "refit": 152.7e6, "tree": 57.1e6, "tree+refit": 122.6e6, "bounds": 16.8e6,
+               "morton": 25.2e6}
 
 STAGE_BYTES = {   # algorithmic bytes per launch (SURVEY.md 8(d) / DESIGN.md), n spheres, m pairs
     "bounds": lambda n, m: 16 * n,
@@ -179,6 +180,7 @@ STAGE_BYTES = {   # algorithmic bytes per launch (SURVEY.md 8(d) / DESIGN.md), n
     "sort": lambda n, m: 68 * n,
     "tree": lambda n, m: 40 * n,
     "refit": lambda n, m: 192 * n,
+    "tree+refit": lambda n, m: 156 * n,   # codes 4 + ids 4 + coords 16 + radii 4 read; nodes 32 + boxes 64 + records 32 written
     "traverse_count": lambda n, m: 36 * n,
     "scan": lambda n, m: 8 * n,
     "traverse_write": lambda n, m: 36 * n + 8 * m,

@@ -39,6 +39,7 @@ SIGNATURES = {
     "col_traverse_atomic": (_int, [_vp, _vp, _u32, _vp, _vp, _int, _u32, _u32, _u32, _vp]),
     "col_build_tree_wide": (_int, [_vp, _vp, _vp, _vp, _vp, _u32, _vp]),
     "col_refit_wide": (_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _int, _u32, _vp]),
+    "col_build_refit_wide": (_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _int, _u32, _vp]),
     "col_traverse_scratch_bytes": (_sz, [_u32, _u64]),
     "col_traverse_wide_count": (_int, [_vp, _vp, _vp, _vp, _vp, _int, _u32, _u32, _u32, _vp]),
     "col_traverse_wide_pairs": (_int, [_vp, _u64, _u64, _vp, _vp, _vp, _vp, _vp, _int, _u32, _u32, _u32, _vp, _vp]),

@@ -18,6 +18,7 @@ Traversal commits pairs either in the deterministic order of the reference's
 work-items run sequentially (count -> scan -> write; the default) or through one
 atomic counter in arbitrary order exactly like upstream (`ordered=False`).
 """
+import os
 import torch
 from numpy import dtype, iinfo
 
@@ -258,6 +259,13 @@ class Collider:
         """Karras tree + leaf boxes + refit, emitting the traversal records."""
         L, P, S = _lib.lib(), _lib.ptr, _lib.stream_ptr(cq)
         n, code, mark = self.size, self.program._code, self._mark
+        if os.environ.get("COL_FUSED_BUILD", "1") != "0":
+            _lib.check(L.col_build_refit_wide(P(self._codes_bufs[1]), P(self._ids_bufs[1]), P(self._nodes_buf),
+                                              P(self._wide_buf), P(self._flags_buf), P(self._bounds_buf),
+                                              P(coords_buf), P(radii_buf), P(self._scene_buf), code, n, S),
+                       "col_build_refit_wide")
+            mark(cq, "tree+refit", 1)
+            return
         _lib.check(L.col_build_tree_wide(P(self._codes_bufs[1]), P(self._ids_bufs[1]), P(self._nodes_buf),
                                          P(self._wide_buf), P(self._flags_buf), n, S), "col_build_tree_wide")
         mark(cq, "tree", 1)

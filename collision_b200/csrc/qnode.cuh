@@ -78,6 +78,17 @@ __device__ __forceinline__ uint32_t max_u16x2(uint32_t a, uint32_t b) {
     asm("max.u16x2 %0, %1, %2;" : "=r"(d) : "r"(a), "r"(b));
     return d;
 }
+__device__ __forceinline__ uint32_t min_u16x2(uint32_t a, uint32_t b) {
+    uint32_t d;
+    asm("min.u16x2 %0, %1, %2;" : "=r"(d) : "r"(a), "r"(b));
+    return d;
+}
+// grid box of the union of two boxes.  grid_coord, floor and ceil are monotone, so they commute
+// with the min / max of the exact merge: the union's lo cells are the smaller lo cells and its
+// ~hi cells the smaller ~hi cells -- one packed minimum per word, no float arithmetic.
+__device__ __forceinline__ uint3 grid_union(const uint3& a, const uint3& b) {
+    return make_uint3(min_u16x2(a.x, b.x), min_u16x2(a.y, b.y), min_u16x2(a.z, b.z));
+}
 // every half-word of the record's box <= the query's  <=>  the grid boxes overlap
 __device__ __forceinline__ bool grid_overlap(const uint3& query, uint32_t r0, uint32_t r1, uint32_t r2) {
     return (max_u16x2(r0, query.x) == query.x) & (max_u16x2(r1, query.y) == query.y) &

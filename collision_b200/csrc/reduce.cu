@@ -114,12 +114,22 @@ reduce_kernel(const T* __restrict__ vals, uint64_t n, T* __restrict__ out, unsig
     __syncthreads();
     if (!is_last) return;
     __threadfence();
-    if (threadIdx.x < NACC * LANES) {
-        const int a = threadIdx.x / LANES;
-        const volatile T* p = partials;
-        T v = p[threadIdx.x];
-        for (unsigned b = 1; b < gridDim.x; b++) v = Op::apply(a, v, p[(size_t)b * NACC * LANES + threadIdx.x]);
-        out[threadIdx.x] = v;
+    // fold the per-block partials with the whole block: thread t owns column t % W and the rows
+    // t / W, t / W + ROWS, ...; the loads are independent (no serial chain of L2 round trips)
+    constexpr int W = NACC * LANES, ROWS = RED_THREADS / W;
+    __shared__ T fold[RED_THREADS];
+    {
+        const int a = (threadIdx.x % W) / LANES;
+        T v = Op::template init<T>(a);
+        for (unsigned b = threadIdx.x / W; b < gridDim.x; b += ROWS)
+            v = Op::apply(a, v, __ldcg(partials + (size_t)b * W + threadIdx.x % W));
+        fold[threadIdx.x] = v;
+        __syncthreads();
+        for (int s = RED_THREADS / 2; s >= W; s >>= 1) {
+            if ((int)threadIdx.x < s) fold[threadIdx.x] = Op::apply(a, fold[threadIdx.x], fold[threadIdx.x + s]);
+            __syncthreads();
+        }
+        if (threadIdx.x < W) out[threadIdx.x] = fold[threadIdx.x];
     }
     if (threadIdx.x == 0) *ticket = 0;  // ready for the next call on this scratch
 }

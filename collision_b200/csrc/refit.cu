@@ -196,6 +196,173 @@ refit_wide_kernel(T* __restrict__ bounds, unsigned char* __restrict__ wide, uint
     }
 }
 
+// ---- tree + refit in one bottom-up pass ----------------------------------------
+// The radix tree over the (code, position) keys is unique, so it can be found from the
+// leaves upwards (Apetrei 2014) instead of by Karras' per-node searches, in the same climb
+// that merges the boxes.  A node covering sorted positions [lo, hi] is the LEFT child of its
+// parent iff its right neighbour shares the longer prefix, delta(hi, hi+1) > delta(lo-1, lo)
+// (delta as collision.cl:55-70, -1 outside the array; the two are never equal inside a sorted
+// array of distinct keys); the parent's split then lies at hi, else at lo-1.  Both children of
+// a node meet on the word flags[split]: the first to arrive leaves the far end of its range
+// there and stops, the second picks it up and so knows the parent's range.
+// Karras' numbering follows from the ranges alone: the left child of a split at g is node g
+// (its hi), the right child node g+1 (its lo), the root node 0 -- so every field of the
+// reference's Node array (collision.cl:72-121) is reproduced: .right_edge = hi, .data = the two
+// children, .parent written by the parent's thread.
+constexpr uint32_t NO_ARRIVAL = 0xFFFFFFFFu;
+
+__device__ __forceinline__ uint32_t exchange_acq_rel(uint32_t* p, uint32_t v) {
+    uint32_t old;
+    asm volatile("atom.exch.acq_rel.gpu.global.b32 %0, [%1], %2;" : "=r"(old) : "l"(p), "r"(v) : "memory");
+    return old;
+}
+__device__ __forceinline__ uint32_t exchange_acq_rel_shared(uint32_t* p, uint32_t v) {
+    uint32_t old;
+    asm volatile("atom.exch.acq_rel.cta.shared.b32 %0, [%1], %2;"
+                 : "=r"(old)
+                 : "r"((uint32_t)__cvta_generic_to_shared(p)), "r"(v)
+                 : "memory");
+    return old;
+}
+// delta of sorted positions a < b (collision.cl:55-70 for in-range arguments)
+__device__ __forceinline__ int key_delta(uint32_t a, uint32_t code_a, uint32_t b, uint32_t code_b) {
+    const uint32_t x = code_a ^ code_b;
+    return x ? __clz(x) : 32 + __clz(a ^ b);
+}
+
+// One block = 256 consecutive sorted leaves [first, last].  A parent all of whose leaves lie in
+// that window is resolved inside the block (boxes and arrival word in shared memory, no global
+// atomic); whether it does is known from the child alone: the parent is the set of keys
+// sharing its prefix, of length delta(split, split+1), with the child, so it reaches past the
+// window's end iff delta(hi, last+1) is at least that long (likewise first-1 on the left).
+template <typename T>
+__global__ void __launch_bounds__(256, 5)
+build_refit_kernel(const uint32_t* __restrict__ codes, const uint32_t* __restrict__ ids, col_node* __restrict__ nodes,
+                   unsigned char* __restrict__ wide, uint32_t* __restrict__ flags, T* __restrict__ bounds,
+                   const T* __restrict__ coords, const T* __restrict__ radii, const T* __restrict__ scene,
+                   uint32_t n) {
+    __shared__ T s_box[256][2][6];          // [split & 255][which child][lo xyz, hi xyz]
+    __shared__ uint32_t s_grid[256][2][3];  // ... and its grid box
+    __shared__ uint32_t s_far[256];         // arrival word of the in-window splits
+    __shared__ uint32_t s_code[258];        // codes of positions first-1 .. last+1
+    const uint32_t first = blockIdx.x * blockDim.x;
+    const uint32_t i = first + threadIdx.x;
+    s_far[threadIdx.x] = NO_ARRIVAL;
+    if (i < n) s_code[threadIdx.x + 1] = __ldg(codes + i);
+    if (threadIdx.x == 0) s_code[0] = first > 0 ? __ldg(codes + first - 1) : 0u;
+    if (threadIdx.x == 32) s_code[257] = first + 256 < n ? __ldg(codes + first + 256) : 0u;
+    __syncthreads();
+    if (i >= n) return;
+    const Quant<T> qz = make_quant(scene);
+    const uint32_t leaf_start = n - 1;
+    const uint32_t last = min(first + 255u, leaf_start);
+    const uint32_t id = __ldg(ids + i);
+    Box<T> box = leaf_box<T>(coords, radii, id);
+    uint32_t self = leaf_start + i;
+    store_box(bounds, self, box);
+    // grid box of the current node: quantised once here (all lanes busy), merged with packed minima on the way up
+    uint3 grid = quantise_box(qz, box.lo, box.hi);
+    {   // leaf record {parent (by the parent's thread), right_edge, id, NO_NODE}
+        uint32_t* rec = reinterpret_cast<uint32_t*>(nodes + self);
+        rec[1] = i;
+        rec[2] = id;
+        rec[3] = 0xFFFFFFFFu;
+    }
+    if (i == 0) nodes[0].parent = 0xFFFFFFFFu;
+    if (n < 2) return;
+    uint32_t lo = i, hi = i;
+    uint32_t code_lo = s_code[threadIdx.x + 1], code_hi = code_lo;
+    // prefix shared with the left / right neighbour of the range (-1: none)
+    int dl = lo > 0 ? key_delta(lo - 1, s_code[threadIdx.x], lo, code_lo) : -1;
+    int dr = hi < leaf_start ? key_delta(hi, code_hi, hi + 1, s_code[threadIdx.x + 2]) : -1;
+    bool local = true;  // the current node lies inside the block's window
+    while (true) {
+        const bool is_left = dr > dl;
+        const uint32_t split = is_left ? hi : lo - 1;
+        if (local) {
+            if (is_left) local = last == leaf_start || key_delta(hi, code_hi, last + 1, s_code[last - first + 2]) < dr;
+            else local = first == 0 || key_delta(first - 1, s_code[0], lo, code_lo) < dl;
+        }
+        Box<T> other;
+        uint3 other_grid;
+        uint32_t far_end, end_code, next_code;  // the sibling's far end, its code, the code one position beyond
+        if (local) {
+            const uint32_t slot = split & 255u;
+            const int half = is_left ? 0 : 1;
+#pragma unroll
+            for (int k = 0; k < 3; k++) {
+                s_box[slot][half][k] = box.lo[k];
+                s_box[slot][half][3 + k] = box.hi[k];
+            }
+            s_grid[slot][half][0] = grid.x;
+            s_grid[slot][half][1] = grid.y;
+            s_grid[slot][half][2] = grid.z;
+            far_end = exchange_acq_rel_shared(&s_far[slot], is_left ? lo : hi);
+            if (far_end == NO_ARRIVAL) return;  // first to arrive: the sibling carries on
+#pragma unroll
+            for (int k = 0; k < 3; k++) {
+                other.lo[k] = s_box[slot][half ^ 1][k];
+                other.hi[k] = s_box[slot][half ^ 1][3 + k];
+            }
+            other_grid = make_uint3(s_grid[slot][half ^ 1][0], s_grid[slot][half ^ 1][1], s_grid[slot][half ^ 1][2]);
+            // all leaves of an in-window parent, and their neighbours, are among the staged codes
+            const uint32_t k = far_end - first + 1;
+            end_code = s_code[k];
+            next_code = s_code[is_left ? k + 1 : k - 1];
+        } else {
+            // my box is in the Bound array before my arrival is visible (release); the sibling's after it (acquire)
+            far_end = exchange_acq_rel(flags + split, is_left ? lo : hi);
+            if (far_end == NO_ARRIVAL) return;
+            const uint32_t sib = is_left ? (far_end == split + 1 ? leaf_start + split + 1 : split + 1)
+                                         : (far_end == split ? leaf_start + split : split);
+            end_code = __ldg(codes + far_end);
+            next_code = is_left ? (far_end < leaf_start ? __ldg(codes + far_end + 1) : 0u)
+                                : (far_end > 0 ? __ldg(codes + far_end - 1) : 0u);
+            other = load_box_cg(bounds, sib);
+            other_grid = quantise_box(qz, other.lo, other.hi);
+        }
+        uint32_t sibling;
+        if (is_left) {
+            sibling = far_end == split + 1 ? leaf_start + split + 1 : split + 1;
+            hi = far_end;
+            code_hi = end_code;
+            dr = hi < leaf_start ? key_delta(hi, code_hi, hi + 1, next_code) : -1;
+        } else {
+            sibling = far_end == split ? leaf_start + split : split;
+            lo = far_end;
+            code_lo = end_code;
+            dl = lo > 0 ? key_delta(lo - 1, next_code, lo, code_lo) : -1;
+        }
+        const bool root = lo == 0 && hi == leaf_start;
+        const uint32_t idx = root ? 0u : (dr > dl ? hi : lo);  // Karras: a left child is numbered by its hi, a right child by its lo
+        const uint32_t child_a = is_left ? self : sibling, child_b = is_left ? sibling : self;
+        {
+            uint32_t* rec = reinterpret_cast<uint32_t*>(nodes + idx);
+            rec[1] = hi;
+            *reinterpret_cast<uint2*>(rec + 2) = make_uint2(child_a, child_b);
+            nodes[child_a].parent = idx;
+            nodes[child_b].parent = idx;
+        }
+        {   // the node's traversal record: children (a leaf as 0x80000000 | position) + their grid boxes
+            const uint3 qa = is_left ? grid : other_grid, qb = is_left ? other_grid : grid;
+            const uint32_t wa = child_a >= leaf_start ? (0x80000000u | (child_a - leaf_start)) : child_a;
+            const uint32_t wb = child_b >= leaf_start ? (0x80000000u | (child_b - leaf_start)) : child_b;
+            unsigned char* rp = wide + (size_t)idx * QNODE_BYTES;
+            *reinterpret_cast<uint4*>(rp) = make_uint4(wa, wb, qa.x, qa.y);
+            *reinterpret_cast<uint4*>(rp + 16) = make_uint4(qa.z, qb.x, qb.y, qb.z);
+        }
+#pragma unroll
+        for (int k = 0; k < 3; k++) {
+            box.lo[k] = vmin(box.lo[k], other.lo[k]);
+            box.hi[k] = vmax(box.hi[k], other.hi[k]);
+        }
+        store_box(bounds, idx, box);
+        if (root) return;
+        grid = grid_union(grid, other_grid);
+        self = idx;
+    }
+}
+
 template <typename T>
 __global__ void __launch_bounds__(256)
 leaf_bounds_kernel(T* __restrict__ bounds, const T* __restrict__ coords, const T* __restrict__ radii,
@@ -242,6 +409,27 @@ COL_API int col_refit_wide(void* bounds, void* wide, uint32_t* flags, const void
         refit_wide_kernel<float><<<blocks, 256, 0, s>>>((float*)bounds, (unsigned char*)wide, flags, (const col_node*)nodes, (const float*)coords4, (const float*)radii, (const float*)scene2x4, n);
     else if (dtype == COL_F64)
         refit_wide_kernel<double><<<blocks, 256, 0, s>>>((double*)bounds, (unsigned char*)wide, flags, (const col_node*)nodes, (const double*)coords4, (const double*)radii, (const double*)scene2x4, n);
+    else
+        return COL_ERR_UNSUPPORTED;
+    COL_CHECK_LAUNCH();
+    return 0;
+}
+
+COL_API int col_build_refit_wide(const uint32_t* codes_sorted, const uint32_t* ids_sorted, void* nodes, void* wide,
+                                 uint32_t* flags, void* bounds, const void* coords4, const void* radii,
+                                 const void* scene2x4, int dtype, uint32_t n, void* stream) {
+    if (!codes_sorted || !ids_sorted || !nodes || !wide || !flags || !bounds || !coords4 || !radii || !scene2x4)
+        return COL_ERR_BAD_ARG;
+    if (scene2x4 == bounds) return COL_ERR_BAD_ARG;  // slot 0 of the Bound array is overwritten with the root box
+    if (n == 0) return 0;
+    if (n > 0x80000000u) return COL_ERR_TOO_LARGE;
+    cudaStream_t s = col_stream(stream);
+    if (n > 1) COL_CUDA(cudaMemsetAsync(flags, 0xFF, sizeof(uint32_t) * ((size_t)n - 1), s));
+    const unsigned blocks = col_blocks(n, 256);
+    if (dtype == COL_F32)
+        build_refit_kernel<float><<<blocks, 256, 0, s>>>(codes_sorted, ids_sorted, (col_node*)nodes, (unsigned char*)wide, flags, (float*)bounds, (const float*)coords4, (const float*)radii, (const float*)scene2x4, n);
+    else if (dtype == COL_F64)
+        build_refit_kernel<double><<<blocks, 256, 0, s>>>(codes_sorted, ids_sorted, (col_node*)nodes, (unsigned char*)wide, flags, (double*)bounds, (const double*)coords4, (const double*)radii, (const double*)scene2x4, n);
     else
         return COL_ERR_UNSUPPORTED;
     COL_CHECK_LAUNCH();

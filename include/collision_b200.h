@@ -188,6 +188,13 @@ int col_build_tree_wide(const uint32_t* codes_sorted, const uint32_t* ids_sorted
                         uint32_t* flags, uint32_t n, void* stream);
 int col_refit_wide(void* bounds, void* wide, uint32_t* flags, const void* nodes, const void* coords4,
                    const void* radii, const void* scene2x4, int dtype, uint32_t n, void* stream);
+/* col_build_tree_wide + col_refit_wide in ONE bottom-up launch (refit.cu): the radix tree is
+ * found from the leaves upwards in the same climb that merges the boxes; Node array, Bound
+ * array and traversal records are bit-identical to the pair above.  `flags` needs no
+ * initialisation (n-1 u32, set by the call). */
+int col_build_refit_wide(const uint32_t* codes_sorted, const uint32_t* ids_sorted, void* nodes, void* wide,
+                         uint32_t* flags, void* bounds, const void* coords4, const void* radii,
+                         const void* scene2x4, int dtype, uint32_t n, void* stream);
 size_t col_traverse_scratch_bytes(uint32_t n_queries, uint64_t capacity);
 int col_traverse_wide_count(uint64_t* total, uint32_t* counts, const void* wide, const void* bounds,
                             const void* scene2x4, int dtype, uint32_t n, uint32_t q_begin, uint32_t q_end,

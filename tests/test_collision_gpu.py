@@ -341,3 +341,51 @@ def test_graph_replay_matches_plain_enqueue(cuda_env, oracle):
     col.get_collisions(cq, coords_d, radii_d, n_buf, pairs_d, cap // 2).synchronize()
     col.get_collisions(cq, coords_d, radii_d, n_buf, pairs_d, cap // 2).synchronize()
     assert (int(n_buf.item()) & 0xFFFFFFFF) == want["total"]
+
+
+@pytest.mark.parametrize("dt", ["float32", "float64"])
+@pytest.mark.parametrize("n,dup", [(1, False), (2, False), (3, True), (257, False), (1000, True), (70001, False),
+                                   (70001, True)])
+def test_fused_build_matches_tree_plus_refit(cuda_env, oracle, n, dup, dt):
+    """col_build_refit_wide (tree found bottom-up inside the refit climb) writes byte-identical
+    Node, Bound and traversal-record arrays to col_build_tree_wide + col_refit_wide (Karras'
+    searches, collision.cl:72-121), and the Node array equals the oracle's -- including runs
+    of equal Morton codes, where the tie-break on the sorted position decides the topology."""
+    import torch
+    from collision_b200 import _lib
+    dev, cq = cuda_env
+    dt = np.dtype(dt)
+    code = _lib.float_code(dt)
+    L, P, S = _lib.lib(), _lib.ptr, cq.cuda_stream
+    rs = np.random.RandomState(n + dup)
+    coords = np.zeros((n, 4), dt)
+    coords[:, :3] = rs.random_sample((n, 3))
+    radii = (rs.random_sample(n) * 0.02).astype(dt)
+    codes = rs.randint(0, 1 << 30, n).astype(np.uint32)
+    if dup:  # long runs of identical codes
+        codes = (codes >> 22) << 22
+        codes[: n // 3] = codes[0]
+    codes.sort()
+    ids = rs.permutation(n).astype(np.uint32)
+    scene = np.zeros((2, 4), dt)
+    scene[1, :3] = 1
+    d_codes, d_ids, d_coords, d_radii, d_scene = map(to_dev, (codes, ids, coords, radii, scene))
+    got = []
+    for fused in (False, True):
+        nodes = torch.full(((2 * n - 1) * 16,), 0xAB, dtype=torch.uint8, device=dev)
+        bounds = torch.zeros((2 * n - 1) * 8 * dt.itemsize, dtype=torch.uint8, device=dev)
+        wide = torch.zeros(max(n - 1, 1) * 32, dtype=torch.uint8, device=dev)
+        flags = torch.full((max(n - 1, 1) * 4,), 0x5A, dtype=torch.uint8, device=dev)
+        if fused:
+            assert L.col_build_refit_wide(P(d_codes), P(d_ids), P(nodes), P(wide), P(flags), P(bounds), P(d_coords),
+                                          P(d_radii), P(d_scene), code, n, S) == 0
+        else:
+            assert L.col_build_tree_wide(P(d_codes), P(d_ids), P(nodes), P(wide), P(flags), n, S) == 0
+            assert L.col_refit_wide(P(bounds), P(wide), P(flags), P(nodes), P(d_coords), P(d_radii), P(d_scene),
+                                    code, n, S) == 0
+        cq.synchronize()
+        got.append((nodes.cpu().numpy(), bounds.cpu().numpy(), wide.cpu().numpy()))
+    for a, b, what in zip(got[0], got[1], ("nodes", "bounds", "records")):
+        assert np.array_equal(a, b), what
+    want = oracle.build_tree(codes, ids, fill=0xFFFFFFFF)   # untouched fields are NO_NODE in both
+    np.testing.assert_equal(got[1][0].view(np.uint32).reshape(-1, 4), want.view(np.uint32).reshape(-1, 4))

@@ -121,6 +121,7 @@ def main():
     report("build tree + wide meta", T(lambda: L.col_build_tree_wide(P(col._codes_bufs[1]), P(col._ids_bufs[1]), P(col._nodes_buf), P(col._wide_buf), P(col._flags_buf), n, S)), 60 * n)
     report("leaf boxes + refit (wide)", T(lambda: L.col_refit_wide(P(col._bounds_buf), P(col._wide_buf), P(col._flags_buf), P(col._nodes_buf), P(coords), P(radii), P(col._scene_buf), code, n, S),
                                           setup=lambda: L.col_build_tree_wide(P(col._codes_bufs[1]), P(col._ids_bufs[1]), P(col._nodes_buf), P(col._wide_buf), P(col._flags_buf), n, S)), 192 * n)
+    report("tree + leaf boxes + refit, one climb", T(lambda: L.col_build_refit_wide(P(col._codes_bufs[1]), P(col._ids_bufs[1]), P(col._nodes_buf), P(col._wide_buf), P(col._flags_buf), P(col._bounds_buf), P(coords), P(radii), P(col._scene_buf), code, n, S)), 156 * n)
     report("traverse wide count", T(lambda: L.col_traverse_wide_count(P(col._total_buf), None, P(col._wide_buf), P(col._bounds_buf), P(col._scene_buf), code, n, 0, n, S)), 36 * n)
     report("traverse wide pairs (walk+scan+emit)", T(lambda: L.col_traverse_wide_pairs(P(pairs), m, 0, P(col._total_buf), P(col._wide_buf), P(col._bounds_buf), P(col._scene_buf), P(col._ids_bufs[1]), code, n, 0, n, P(scr_), S)), 36 * n + 8 * m)
     torch.cuda.synchronize()
