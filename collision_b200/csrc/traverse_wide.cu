@@ -251,30 +251,78 @@ confirm_kernel(unsigned long long* __restrict__ total, uint32_t* __restrict__ co
 // (query-major, DFS order: the order of the reference's work-items run sequentially).
 // Parked hits are simply copied (ids gathered); a query with more than `depth` hits
 // walks again for the remainder only.
+#ifndef COL_EMIT_CHUNK
+#define COL_EMIT_CHUNK 8
+#endif
+constexpr uint32_t EMIT_CHUNK = COL_EMIT_CHUNK;   // parked rows per query moved per round
+
 template <typename T>
 __global__ void __launch_bounds__(TRV_THREADS)
 emit_kernel(uint32_t* __restrict__ pairs, uint64_t capacity, uint64_t base, const uint32_t* __restrict__ offsets,
             const unsigned long long* __restrict__ total, const uint32_t* __restrict__ stash,
             const unsigned char* __restrict__ wide, const T* __restrict__ bounds, const T* __restrict__ scene,
             const uint32_t* __restrict__ ids, uint32_t n, uint32_t q_begin, uint32_t q_end, uint32_t depth) {
+    // A warp owns 32 consecutive queries, whose rows are (nearly) one contiguous piece of the
+    // list.  Per round every lane gathers up to EMIT_CHUNK of its parked rows (coalesced
+    // k-major reads) into the warp's shared-memory strip IN LIST ORDER; the strip then goes
+    // out with full-width stores instead of one 8-byte store per lane into 32 different sectors.
+    __shared__ uint32_t s_other[TRV_THREADS / 32][32 * EMIT_CHUNK];
+    __shared__ unsigned char s_owner[TRV_THREADS / 32][32 * EMIT_CHUNK];
     const uint32_t i = blockIdx.x * TRV_THREADS + threadIdx.x;
-    const uint32_t q = q_begin + i;
-    if (q >= q_end) return;
     const uint32_t nq = q_end - q_begin;
-    const uint32_t off = offsets[i];
-    const uint32_t next = (i + 1 < nq) ? offsets[i + 1] : (uint32_t)*total;
-    const uint32_t hits = next - off;
-    const uint64_t out = base + off;
-    if (hits == 0 || out >= capacity) return;
-    const uint32_t qid = __ldg(ids + q);
-    const uint32_t parked = min(hits, depth);
-    for (uint32_t k = 0; k < parked; k++) {
-        const uint64_t at = out + k;
-        if (at < capacity)
-            *reinterpret_cast<uint2*>(pairs + at * 2) = make_uint2(qid, __ldg(ids + __ldg(stash + (size_t)k * nq + i)));
+    const unsigned warp = threadIdx.x >> 5, lane = lane_id();
+    const bool live = i < nq;
+    const uint32_t q = q_begin + i;
+    uint32_t off = 0, hits = 0, qid = 0;
+    if (live) {
+        off = offsets[i];
+        hits = ((i + 1 < nq) ? offsets[i + 1] : (uint32_t)*total) - off;
+        if (base + off >= capacity) hits = 0;
+        qid = __ldg(ids + q);
     }
-    if (hits > depth) {
+    const uint32_t parked = min(hits, depth);
+    const uint32_t most = __reduce_max_sync(0xffffffffu, parked);
+    for (uint32_t k0 = 0; k0 < most; k0 += EMIT_CHUNK) {
+        const uint32_t mine = parked > k0 ? min(parked - k0, EMIT_CHUNK) : 0u;   // my rows this round
+        uint32_t start = mine;                                                     // -> exclusive prefix over the lanes
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t up = __shfl_up_sync(0xffffffffu, start, o);
+            if (lane >= (unsigned)o) start += up;
+        }
+        const uint32_t rows = __shfl_sync(0xffffffffu, start, 31);
+        start -= mine;
+        {   // all loads of the round in flight together: positions, then ids, then the strip
+            uint32_t pos[EMIT_CHUNK], other[EMIT_CHUNK];
+#pragma unroll
+            for (uint32_t k = 0; k < EMIT_CHUNK; k++)
+                if (k < mine) pos[k] = __ldg(stash + (size_t)(k0 + k) * nq + i);
+#pragma unroll
+            for (uint32_t k = 0; k < EMIT_CHUNK; k++)
+                if (k < mine) other[k] = __ldg(ids + pos[k]);
+#pragma unroll
+            for (uint32_t k = 0; k < EMIT_CHUNK; k++)
+                if (k < mine) {
+                    s_other[warp][start + k] = other[k];
+                    s_owner[warp][start + k] = (unsigned char)lane;
+                }
+        }
+        __syncwarp();
+        for (uint32_t f0 = 0; f0 < rows; f0 += 32) {
+            const uint32_t f = f0 + lane;
+            const bool on = f < rows;
+            const unsigned owner = on ? s_owner[warp][f] : 0u;
+            const uint32_t o_start = __shfl_sync(0xffffffffu, start, owner);
+            const uint32_t o_off = __shfl_sync(0xffffffffu, off, owner);
+            const uint32_t o_qid = __shfl_sync(0xffffffffu, qid, owner);
+            const uint64_t at = base + o_off + k0 + (f - o_start);
+            if (on && at < capacity) *reinterpret_cast<uint2*>(pairs + at * 2) = make_uint2(o_qid, s_other[warp][f]);
+        }
+        __syncwarp();
+    }
+    if (hits > depth) {   // the rows beyond the stash: walk again, exactly
         const uint32_t leaf_start = n - 1;
+        const uint64_t out = base + off;
         const Query<T> query = load_query(bounds, leaf_start + q, make_quant(scene));
         walk<true>(wide, bounds, query, q, leaf_start, [=](uint32_t pos, uint32_t k, bool) {
             const uint64_t at = out + k;

@@ -42,6 +42,21 @@ def test_scratch_queries_are_pure_host():
     assert L.col_reduce_scratch_bytes() > 0
 
 
+def test_c_example_compiles_against_the_header():
+    """examples/pipeline.c (the call sequence INTEGRATION.md shows a C host) type-checks against
+    the header as C99 with warnings as errors, and links against the built library."""
+    import subprocess
+    import tempfile
+    from collision_b200 import _lib
+    src = ROOT / "examples" / "pipeline.c"
+    with tempfile.TemporaryDirectory() as tmp:
+        obj = Path(tmp) / "pipeline.so"
+        subprocess.run(["gcc", "-std=c99", "-Wall", "-Wextra", "-Werror", "-shared", "-fPIC", "-I", str(ROOT / "include"),
+                        str(src), "-o", str(obj), "-L", str(_lib.lib_path().parent), "-l:" + _lib.lib_path().name,
+                        "-Wl,--no-undefined", "-Wl,--allow-shlib-undefined"], check=True, capture_output=True)
+        assert obj.exists()
+
+
 def test_sm100a_only():
     import subprocess
     from collision_b200 import _lib
