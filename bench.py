@@ -169,10 +169,10 @@ def run_reference(args):
 
 # ---------------------------------------------------------------- our arm
 # dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu --set full
-# capture of this workload (profiles/r1c_ncu_full_summary.txt; cold cache under ncu):
-# candidates 112.4 + confirm 78.9 + scan 8.4 + emit 49.4 MB
-NCU_TRAFFIC = {"traverse_pairs": 249.1e6, "refit": 152.7e6, "tree": 57.1e6, "tree+refit": 122.6e6, "bounds": 16.8e6,
-               "morton": 25.2e6}
+# capture of this workload (profiles/r1d_ncu_full_summary.txt; cold cache under ncu):
+# candidates 110.2 + confirm 89.4 + scan 4.2 + emit 49.2 MB
+NCU_TRAFFIC = {"traverse_pairs": 253.0e6, "tree+refit": 120.4e6, "bounds": 16.8e6, "morton": 16.8e6,
+               "refit": 152.7e6, "tree": 57.1e6}   # (the last two: the two-launch build, profiles/r1c_*)
 
 STAGE_BYTES = {   # algorithmic bytes per launch (SURVEY.md 8(d) / DESIGN.md), n spheres, m pairs
     "bounds": lambda n, m: 16 * n,
