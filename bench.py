@@ -236,6 +236,21 @@ def run_ours(args):
 
     kw = {"sync_totals": False} if world > 1 else {}
 
+    # which spheres this rank uploads each step: all of them on one GPU; at N > 1 the rank's own
+    # slice in mode "gather_inputs" (k host links feed the all-gather), else rank 0 the whole scene
+    if world == 1:
+        mine = (0, n)
+    elif args.multi_gpu_mode == "gather_inputs":
+        from collision_b200.sharded import shard_range
+        mine = shard_range(n, world, rank)
+    else:
+        mine = (0, n) if rank == 0 else None
+
+    def upload(coords_dst, radii_dst):
+        if mine is not None:
+            coords_dst[mine[0]:mine[1]].copy_(coords_pin[mine[0]:mine[1]], non_blocking=True)
+            radii_dst[mine[0]:mine[1]].copy_(radii_pin[mine[0]:mine[1]], non_blocking=True)
+
     def step():
         return collider.get_collisions(cq, coords_d, radii_d, n_buf, pairs_d, local_cap, **kw)
 
@@ -308,9 +323,7 @@ def run_ours(args):
         torch.cuda.synchronize()
         t0 = time.perf_counter()
         with torch.cuda.stream(cq):
-            if rank == 0:   # the scene lives in rank 0's host memory; the other ranks receive it over NVLink
-                coords_d.copy_(coords_pin, non_blocking=True)
-                radii_d.copy_(radii_pin, non_blocking=True)
+            upload(coords_d, radii_d)
             collider.get_collisions(cq, coords_d, radii_d, n_buf, pairs_d, local_cap, **kw)
             n_pin.copy_(n_buf, non_blocking=True)
         cq.synchronize()
@@ -343,9 +356,7 @@ def run_ours(args):
             with torch.cuda.stream(up):
                 if computed[b] is not None:
                     up.wait_event(computed[b])          # inputs of step i-2 no longer needed
-                if rank == 0:
-                    coords_db[b].copy_(coords_pin, non_blocking=True)
-                    radii_db[b].copy_(radii_pin, non_blocking=True)
+                upload(coords_db[b], radii_db[b])
                 uploaded = torch.cuda.Event()
                 uploaded.record(up)
             if downloaded[b] is not None:
@@ -414,12 +425,18 @@ def run_ours(args):
             "data": "synthetic",
             "config": workload_config(n, {"launch": "CUDA graph replay" if (world == 1 and not args.no_graph) else "kernel by kernel",
                                           "parallelism": "single GPU" if world == 1 else
-                                          "{}: traversal sharded over {} contiguous Morton ranges, NCCL "
-                                          "broadcast + all_gather of row totals".format(args.multi_gpu_mode, world)}),
+                                          "{}: {}, traversal sharded over {} contiguous Morton ranges, NCCL "
+                                          "all_gather of row totals".format(
+                                              args.multi_gpu_mode,
+                                              {"gather_inputs": "scene all-gathered over NVLink from per-rank slices, "
+                                                                "build replicated",
+                                               "replicate_build": "scene broadcast from rank 0, build replicated",
+                                               "broadcast_tree": "tree built on rank 0 and broadcast"}[args.multi_gpu_mode],
+                                              world)}),
             "pairs": total, "pairs_per_sec": total / (ms_per_step * 1e-3),
             "e2e": {"value": n / e2e_sec, "unit": UNIT,
                     "h2d_bytes_per_step": coords_pin.numel() * 4 + radii_pin.numel() * 4,
-                    "d2h_bytes_per_step": 4 + local_cap * 8, "ms_per_step": e2e_sec * 1e3,
+                    "d2h_bytes_per_step": 4 * world + total * 8, "ms_per_step": e2e_sec * 1e3,
                     "how": "stream of frames: upload / compute / download of consecutive steps overlap "
                            "(double-buffered), every step copies its inputs H2D and its count + rows D2H",
                     "single_step_latency_ms": e2e_latency * 1e3},
@@ -440,7 +457,7 @@ def main():
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
     ap.add_argument("--no-graph", action="store_true", help="enqueue kernel by kernel instead of replaying a CUDA graph")
-    ap.add_argument("--multi-gpu-mode", choices=["broadcast_tree", "replicate_build"], default="replicate_build",
+    ap.add_argument("--multi-gpu-mode", choices=["broadcast_tree", "replicate_build", "gather_inputs"], default="gather_inputs",
                     help="N>1: broadcast the tree built on rank 0 (north_star) or the inputs and build everywhere")
     args = ap.parse_args()
     if args.impl == "reference":

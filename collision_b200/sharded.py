@@ -43,16 +43,36 @@ def broadcast_buffers(buffers, src=0, group=None):
         dist.broadcast(b, src=src, group=group)
 
 
+def gather_slices(buf, per_item, n, group=None):
+    """In-place all-gather of a scene array: `buf` holds n items of `per_item` elements and rank
+    r has filled items [n*r/k, n*(r+1)/k) (shard_range); afterwards every rank holds all n."""
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    flat = buf.view(-1)
+    if n % world == 0:
+        m = n // world * per_item
+        mine = flat[rank * m:(rank + 1) * m]
+        # NCCL gathers in place when the input is the rank's own piece of the output; other
+        # backends get a private copy of the piece
+        dist.all_gather_into_tensor(flat[:n * per_item], mine if flat.is_cuda else mine.clone(), group=group)
+    else:   # ragged shards: one broadcast per owner
+        for r in range(world):
+            b, e = shard_range(n, world, r)
+            if e > b:
+                dist.broadcast(flat[b * per_item:e * per_item], src=r, group=group)
+
+
 class ShardedCollider:
     """Collider.get_collisions across `world` GPUs.  Same call signature; rank `src`
     passes the scene (`coords_buf`, `radii_buf`); in mode "broadcast_tree" the other
-    ranks may pass None, in mode "replicate_build" they pass buffers to receive it.
+    ranks may pass None, in mode "replicate_build" they pass buffers to receive it; in mode
+    "gather_inputs" every rank passes full-size buffers of which it has filled its own slice
+    of the spheres (`shard_range(size, world, rank)` in input order).
 
     After a call: `n_collisions_buf[0]` = global row count (low 32 bits, like the
     reference's counter) on every rank, `collisions_buf` = this rank's rows
     (`local_pairs` of them, global row index `pair_base` + i)."""
 
-    MODES = ("broadcast_tree", "replicate_build")
+    MODES = ("broadcast_tree", "replicate_build", "gather_inputs")
 
     def __init__(self, ctx, size, ngroups, group_size, coord_dtype=dtype('float32'), group=None, src=0,
                  mode="broadcast_tree"):
@@ -61,7 +81,10 @@ class ShardedCollider:
         mode "replicate_build": the INPUT (coords + radii, 20 B per sphere) is broadcast
         from `src` and every rank builds the identical tree itself -- the build is
         deterministic and bit-exact, so the result is the same; it trades redundant
-        compute for 3.4x less NVLink traffic and no serial rank-0 phase."""
+        compute for 3.4x less NVLink traffic and no serial rank-0 phase.
+        mode "gather_inputs": as "replicate_build", but the scene arrives sharded -- every rank
+        owns the spheres [size*r/k, size*(r+1)/k) -- and is all-gathered in place (the same
+        bytes over NVLink, but k host links feed it instead of one)."""
         if mode not in self.MODES:
             raise ValueError("mode must be one of {}".format(self.MODES))
         self.mode = mode
@@ -114,7 +137,11 @@ class ShardedCollider:
                 broadcast_buffers(self._shared_buffers(), self.src, self.group)
                 c._mark(cq, "broadcast", 0)
             else:
-                broadcast_buffers([coords_buf, radii_buf], self.src, self.group)
+                if self.mode == "gather_inputs":
+                    gather_slices(coords_buf, 4, self.size, self.group)
+                    gather_slices(radii_buf, 1, self.size, self.group)
+                else:
+                    broadcast_buffers([coords_buf, radii_buf], self.src, self.group)
                 c._mark(cq, "broadcast", 0)
                 c._sort_stage(cq, coords_buf)
                 c._build_wide(cq, coords_buf, radii_buf)

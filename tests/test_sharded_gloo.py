@@ -75,3 +75,34 @@ def test_shard_range_properties():
             assert all(a[1] == b[0] for a, b in zip(edges, edges[1:]))
             sizes = [e - b for b, e in edges]
             assert max(sizes) - min(sizes) <= 1
+
+
+def _gather_worker(rank, world, port, n, tmpdir):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from collision_b200.sharded import gather_slices, shard_range
+        c, r = G.random_spheres(n)
+        b, e = shard_range(n, world, rank)
+        # every rank fills only its own spheres; the rest is poison
+        coords = torch.full((n, 4), float("nan"), dtype=torch.float32)
+        radii = torch.full((n,), float("nan"), dtype=torch.float32)
+        coords[b:e] = torch.from_numpy(c[b:e])
+        radii[b:e] = torch.from_numpy(r[b:e].astype(np.float32))
+        gather_slices(coords, 4, n)
+        gather_slices(radii, 1, n)
+        np.save(os.path.join(tmpdir, "coords{}.npy".format(rank)), coords.numpy())
+        np.save(os.path.join(tmpdir, "radii{}.npy".format(rank)), radii.numpy())
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("n", [1001, 4096])   # ragged shards (one broadcast per owner) and equal ones (all-gather)
+def test_two_rank_input_gather(tmp_path, n):
+    """mode "gather_inputs": the scene arrives sharded by sphere index and is all-gathered in place."""
+    world = 2
+    mp.spawn(_gather_worker, args=(world, _free_port(), n, str(tmp_path)), nprocs=world, join=True)
+    c, r = G.random_spheres(n)
+    for k in range(world):
+        np.testing.assert_equal(np.load(tmp_path / "coords{}.npy".format(k)), c.astype(np.float32))
+        np.testing.assert_equal(np.load(tmp_path / "radii{}.npy".format(k)), r.astype(np.float32))
