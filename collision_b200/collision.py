@@ -18,7 +18,6 @@ Traversal commits pairs either in the deterministic order of the reference's
 work-items run sequentially (count -> scan -> write; the default) or through one
 atomic counter in arbitrary order exactly like upstream (`ordered=False`).
 """
-import os
 import torch
 from numpy import dtype, iinfo
 
@@ -109,9 +108,12 @@ class Collider:
 
     def __init__(self, ctx, size, ngroups, group_size, coord_dtype=dtype('float32'),
                  program=None, sorter_programs=(None, None), reducer_program=None, ordered=True,
-                 layout="wide", graph=False):
+                 layout="wide", graph=False, fused_build=True):
         coord_dtype = dtype(coord_dtype)
         self.size = size
+        # True: tree + leaf boxes + refit in one bottom-up launch (col_build_refit_wide);
+        # False: Karras' searches, then the climb (col_build_tree_wide + col_refit_wide) -- same arrays
+        self.fused_build = fused_build
         self.group_size = group_size
         self.ordered = ordered
         # "wide": traversal records + single-pass compaction (default, needs ordered=True);
@@ -259,7 +261,7 @@ class Collider:
         """Karras tree + leaf boxes + refit, emitting the traversal records."""
         L, P, S = _lib.lib(), _lib.ptr, _lib.stream_ptr(cq)
         n, code, mark = self.size, self.program._code, self._mark
-        if os.environ.get("COL_FUSED_BUILD", "1") != "0":
+        if self.fused_build:
             _lib.check(L.col_build_refit_wide(P(self._codes_bufs[1]), P(self._ids_bufs[1]), P(self._nodes_buf),
                                               P(self._wide_buf), P(self._flags_buf), P(self._bounds_buf),
                                               P(coords_buf), P(radii_buf), P(self._scene_buf), code, n, S),

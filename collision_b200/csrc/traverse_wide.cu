@@ -18,7 +18,6 @@
 //    a second time, for the remainder.  (A single fused kernel chaining blocks by
 //    decoupled look-back was measured slower: blocks of dense regions stall every
 //    later block, and a shared-memory stash shrinks the L1 the walk depends on.)
-#include <cstdlib>
 
 #include "common.cuh"
 #include "qnode.cuh"
@@ -410,7 +409,7 @@ static int pairs_impl(uint32_t* pairs, uint64_t capacity, uint64_t base, unsigne
     uint32_t* counts = reinterpret_cast<uint32_t*>(sc + L.counts);
     uint32_t* stash = reinterpret_cast<uint32_t*>(sc + L.stash);
     const unsigned blocks = col_blocks(nq, TRV_THREADS);
-    static const uint32_t pf = getenv("COL_TRV_PF") ? atoi(getenv("COL_TRV_PF")) : 64;
+    const uint32_t pf = 64;   // 128-byte lines of the block's own record window prefetched to L1 (0..256: +4 % at 64)
     candidates_kernel<T><<<blocks, TRV_THREADS, 0, s>>>(counts, stash, w, bounds, scene, n, q_begin, q_end, pf, depth);
     COL_CHECK_LAUNCH();
     confirm_kernel<T><<<blocks, TRV_THREADS, 0, s>>>(total, counts, stash, w, bounds, scene, n, q_begin, q_end, depth);

@@ -389,3 +389,17 @@ def test_fused_build_matches_tree_plus_refit(cuda_env, oracle, n, dup, dt):
         assert np.array_equal(a, b), what
     want = oracle.build_tree(codes, ids, fill=0xFFFFFFFF)   # untouched fields are NO_NODE in both
     np.testing.assert_equal(got[1][0].view(np.uint32).reshape(-1, 4), want.view(np.uint32).reshape(-1, 4))
+
+
+def test_collider_two_launch_build(cuda_env, oracle):
+    """Collider(fused_build=False) -- Karras' searches, then the climb -- gives the same rows."""
+    from collision_b200.collision import Collider
+    dev, cq = cuda_env
+    n = 6000
+    c, r = G.random_spheres(n)
+    want = oracle.collide(c, r)
+    for fused in (True, False):
+        col = Collider(dev, n, 8, 64, fused_build=fused)
+        total, pairs = run_collider(cuda_env, col, c, r, want["total"], np.dtype("float32"))
+        assert total == want["total"]
+        np.testing.assert_equal(pairs, want["pairs"])

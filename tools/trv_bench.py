@@ -14,13 +14,14 @@ ap.add_argument("--n", type=int, default=1 << 20)
 ap.add_argument("--reps", type=int, default=5)
 ap.add_argument("--clustered", action="store_true")
 ap.add_argument("--no-flush", action="store_true")
+ap.add_argument("--two-launch-build", action="store_true")
 args = ap.parse_args()
 dev = torch.device("cuda", 0)
 L, P = _lib.lib(), _lib.ptr
 cq = torch.cuda.current_stream(); S = cq.cuda_stream
 n = args.n
 coords, radii = (gen_clustered if args.clustered else gen_uniform)(n, dev)
-col = Collider(dev, n, 8, 128)
+col = Collider(dev, n, 8, 128, fused_build=not args.two_launch_build)
 n_buf = torch.zeros(1, dtype=torch.int32, device=dev)
 col.get_collisions(cq, coords, radii, n_buf, None, 0).synchronize()
 m = int(n_buf.item()) & 0xFFFFFFFF
