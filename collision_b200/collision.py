@@ -165,7 +165,9 @@ class Collider:
         self._nodes_buf = _lib.alloc_bytes(ctx, self.n_nodes * Node.itemsize)
         # dual use: scene bounds first, per-node boxes afterwards (collision.py:74-78)
         self._bounds_buf = _lib.alloc_bytes(ctx, max(self.n_nodes, 2) * 2 * 4 * self.program.coord_dtype.itemsize)
-        self._flags_buf = _lib.alloc_bytes(ctx, self.n_nodes * 4)
+        # arrival words (upstream: one u32 per node); the fused build wants 2N words (N-1 arrival
+        # words of the cross-window splits + N hand-over slots between its two passes)
+        self._flags_buf = _lib.alloc_bytes(ctx, (self.n_nodes + 1) * 4)
         self._counts_buf = _lib.alloc_bytes(ctx, self.size * 4)
         self._scan_scratch = _lib.alloc_bytes(ctx, L.col_scan_scratch_bytes(self.size))
         self._total_buf = torch.zeros(1, dtype=torch.int64, device=ctx)
@@ -266,7 +268,7 @@ class Collider:
                                               P(self._wide_buf), P(self._flags_buf), P(self._bounds_buf),
                                               P(coords_buf), P(radii_buf), P(self._scene_buf), code, n, S),
                        "col_build_refit_wide")
-            mark(cq, "tree+refit", 1)
+            mark(cq, "tree+refit", 2 if n >= (1 << 22) else 1)   # (large scenes: window pass + top pass)
             return
         _lib.check(L.col_build_tree_wide(P(self._codes_bufs[1]), P(self._ids_bufs[1]), P(self._nodes_buf),
                                          P(self._wide_buf), P(self._flags_buf), n, S), "col_build_tree_wide")

@@ -14,7 +14,7 @@ struct col_buffers {
     void* nodes;           /* 16 * (2n-1) bytes: the Node array   */
     float* bounds;         /* 32 * (2n-1) bytes: the Bound array  */
     void* wide;            /* 32 * (n-1) bytes: traversal records */
-    uint32_t* flags;       /* 4 * (n-1) bytes: arrival words      */
+    uint32_t* flags;       /* 4 * 2n bytes: build scratch          */
     uint32_t* pairs;       /* capacity x 2 u32 rows               */
     uint64_t* total;       /* 1 u64: true number of pairs         */
     void *reduce_scratch, *sort_scratch, *traverse_scratch;

@@ -188,10 +188,11 @@ int col_build_tree_wide(const uint32_t* codes_sorted, const uint32_t* ids_sorted
                         uint32_t* flags, uint32_t n, void* stream);
 int col_refit_wide(void* bounds, void* wide, uint32_t* flags, const void* nodes, const void* coords4,
                    const void* radii, const void* scene2x4, int dtype, uint32_t n, void* stream);
-/* col_build_tree_wide + col_refit_wide in ONE bottom-up launch (refit.cu): the radix tree is
- * found from the leaves upwards in the same climb that merges the boxes; Node array, Bound
- * array and traversal records are bit-identical to the pair above.  `flags` needs no
- * initialisation (n-1 u32, set by the call). */
+/* col_build_tree_wide + col_refit_wide as ONE bottom-up climb (refit.cu): the radix tree is found
+ * from the leaves upwards in the same climb that merges the boxes -- a pass over the 256-leaf
+ * windows (shared-memory arrivals), then a pass over the few nodes that span windows.  Node
+ * array, Bound array and traversal records are bit-identical to the pair above.
+ * `flags`: 2n u32 of scratch, set by the call (n-1 arrival words + n hand-over slots). */
 int col_build_refit_wide(const uint32_t* codes_sorted, const uint32_t* ids_sorted, void* nodes, void* wide,
                          uint32_t* flags, void* bounds, const void* coords4, const void* radii,
                          const void* scene2x4, int dtype, uint32_t n, void* stream);

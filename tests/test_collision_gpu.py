@@ -345,7 +345,7 @@ def test_graph_replay_matches_plain_enqueue(cuda_env, oracle):
 
 @pytest.mark.parametrize("dt", ["float32", "float64"])
 @pytest.mark.parametrize("n,dup", [(1, False), (2, False), (3, True), (257, False), (1000, True), (70001, False),
-                                   (70001, True)])
+                                   (70001, True), ((1 << 22) + 5, False)])   # (the last: two-pass form of the fused build)
 def test_fused_build_matches_tree_plus_refit(cuda_env, oracle, n, dup, dt):
     """col_build_refit_wide (tree found bottom-up inside the refit climb) writes byte-identical
     Node, Bound and traversal-record arrays to col_build_tree_wide + col_refit_wide (Karras'
@@ -375,7 +375,8 @@ def test_fused_build_matches_tree_plus_refit(cuda_env, oracle, n, dup, dt):
         nodes = torch.full(((2 * n - 1) * 16,), 0xAB, dtype=torch.uint8, device=dev)
         bounds = torch.zeros((2 * n - 1) * 8 * dt.itemsize, dtype=torch.uint8, device=dev)
         wide = torch.zeros(max(n - 1, 1) * 32, dtype=torch.uint8, device=dev)
-        flags = torch.full((max(n - 1, 1) * 4,), 0x5A, dtype=torch.uint8, device=dev)
+        flags = torch.full((2 * n * 4,), 0x5A, dtype=torch.uint8, device=dev)   # (the fused call wants 2n words)
+        cq.wait_stream(torch.cuda.current_stream(dev))   # the fills above run on torch's current stream
         if fused:
             assert L.col_build_refit_wide(P(d_codes), P(d_ids), P(nodes), P(wide), P(flags), P(bounds), P(d_coords),
                                           P(d_radii), P(d_scene), code, n, S) == 0
