@@ -169,9 +169,9 @@ def run_reference(args):
 
 # ---------------------------------------------------------------- our arm
 # dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu --set full
-# capture of this workload (profiles/r1d_ncu_full_summary.txt; cold cache under ncu):
-# candidates 110.2 + confirm 89.4 + scan 4.2 + emit 49.2 MB
-NCU_TRAFFIC = {"traverse_pairs": 253.0e6, "tree+refit": 120.4e6, "bounds": 16.8e6, "morton": 16.8e6,
+# capture of this workload (profiles/r1e_ncu_full_summary.txt; cold cache under ncu):
+# candidates 108.7 + confirm 89.5 + scan 4.2 + emit 48.8 MB
+NCU_TRAFFIC = {"traverse_pairs": 251.2e6, "tree+refit": 122.7e6, "bounds": 16.8e6, "morton": 16.8e6,
                "refit": 152.7e6, "tree": 57.1e6}   # (the last two: the two-launch build, profiles/r1c_*)
 
 STAGE_BYTES = {   # algorithmic bytes per launch (SURVEY.md 8(d) / DESIGN.md), n spheres, m pairs
