@@ -226,12 +226,22 @@ confirm_kernel(unsigned long long* __restrict__ total, uint32_t* __restrict__ co
                 Query<T> query;
 #pragma unroll
                 for (int k = 0; k < 3; k++) { query.lo[k] = b.lo[k]; query.hi[k] = b.hi[k]; }
+                // software pipeline: position k+2 and box k+1 are in flight while box k is tested (the
+                // compaction writes slot hits <= k, behind every slot still to be read)
+                uint32_t p0 = park[0], p1 = cand > 1 ? park[nq] : 0u;
+                LeafBox<T> b0 = load_leaf_box(bounds, leaf_start + p0);
                 for (uint32_t k = 0; k < cand; k++) {
-                    const uint32_t pos = park[(size_t)k * nq];
-                    if (exact_overlap(query, load_leaf_box(bounds, leaf_start + pos))) {
-                        park[(size_t)hits * nq] = pos;
+                    LeafBox<T> b1 = b0;
+                    uint32_t p2 = 0;
+                    if (k + 1 < cand) b1 = load_leaf_box(bounds, leaf_start + p1);
+                    if (k + 2 < cand) p2 = park[(size_t)(k + 2) * nq];
+                    if (exact_overlap(query, b0)) {
+                        park[(size_t)hits * nq] = p0;
                         hits++;
                     }
+                    p0 = p1;
+                    p1 = p2;
+                    b0 = b1;
                 }
             } else {
                 const Query<T> query = load_query(bounds, leaf_start + q, make_quant(scene));
