@@ -14,6 +14,7 @@ _LIB_PATH = _HERE / "libcollision_b200.so"
 _lib = None
 
 COL_F32, COL_F64 = 0, 1
+COL_U32, COL_I32, COL_U64, COL_I64 = 2, 3, 4, 5
 
 _vp, _u64, _u32, _int, _sz = C.c_void_p, C.c_uint64, C.c_uint32, C.c_int, C.c_size_t
 
@@ -148,3 +149,15 @@ def float_code(dt):
     if dt == np.float64:
         return COL_F64
     raise ValueError("Invalid dtype: {}".format(dt))
+
+
+_VALUE_CODES = {"float32": COL_F32, "float64": COL_F64, "uint32": COL_U32, "int32": COL_I32,
+                "uint64": COL_U64, "int64": COL_I64}
+
+
+def value_code(dt):
+    """Value-type code of the reductions (floats for min/max, floats and integers for sums)."""
+    name = np.dtype(dt).base.name
+    if name not in _VALUE_CODES:
+        raise ValueError("Invalid dtype: {}".format(name))
+    return _VALUE_CODES[name]

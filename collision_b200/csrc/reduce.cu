@@ -173,5 +173,11 @@ COL_API int col_sum(const void* values, uint64_t n, int dtype, uint32_t lanes, v
     if (!values || !out_sum || !scratch) return COL_ERR_BAD_ARG;
     if (dtype == COL_F32) return launch_reduce<float, OpSum>(values, n, lanes, out_sum, scratch, col_stream(stream));
     if (dtype == COL_F64) return launch_reduce<double, OpSum>(values, n, lanes, out_sum, scratch, col_stream(stream));
+    // integer sums wrap modulo 2^32 / 2^64 (OpenCL integer arithmetic: two's complement for the signed
+    // types as well), so the unsigned instantiation serves both and the result is exact for any order
+    if (dtype == COL_U32 || dtype == COL_I32)
+        return launch_reduce<uint32_t, OpSum>(values, n, lanes, out_sum, scratch, col_stream(stream));
+    if (dtype == COL_U64 || dtype == COL_I64)
+        return launch_reduce<unsigned long long, OpSum>(values, n, lanes, out_sum, scratch, col_stream(stream));
     return COL_ERR_UNSUPPORTED;
 }

@@ -21,11 +21,12 @@ np_float_dtypes = set(map(dtype, _float_names))
 class ReductionProgram(Program):
     accumulator = []          # [(initialiser, function)], as upstream
     _entry = None             # name of the C-ABI entry point
+    _value_bases = ('float32', 'float64')   # scalar types the entry point is instantiated for
 
     def __init__(self, ctx, value_dtype):
         self.value_dtype = dtype(value_dtype)
         self.acc_dtype = dtype((self.value_dtype, len(self.accumulator)))
-        if self.value_dtype.base not in (dtype('float32'), dtype('float64')):
+        if self.value_dtype.base.name not in self._value_bases:
             raise ValueError("Invalid dtype: {}".format(self.value_dtype))
         dtype_sizeof(self.value_dtype)   # validates the vector width
         super().__init__(ctx)
@@ -61,7 +62,7 @@ class Reducer:
     def reduce(self, cq, size, values_buf, output_buf, wait_for=None):
         _lib.begin(cq, wait_for)
         fn = getattr(_lib.lib(), self.program._entry)
-        _lib.check(fn(_lib.ptr(values_buf), size, _lib.float_code(self.program.value_dtype),
+        _lib.check(fn(_lib.ptr(values_buf), size, _lib.value_code(self.program.value_dtype),
                       dtype_lanes(self.program.value_dtype), _lib.ptr(output_buf),
                       _lib.ptr(self._ensure_scratch()), _lib.stream_ptr(cq)), self.program._entry)
         return _lib.done(cq)

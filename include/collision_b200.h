@@ -31,6 +31,11 @@ extern "C" {
 
 #define COL_F32 0
 #define COL_F64 1
+/* integer value types of col_sum (tests/test_summer_py.py:12 sums uint32x4 and int32) */
+#define COL_U32 2
+#define COL_I32 3
+#define COL_U64 4
+#define COL_I64 5
 
 #define COL_ERR_BAD_ARG (-1)
 #define COL_ERR_TOO_LARGE (-2)
@@ -61,7 +66,8 @@ typedef struct {
  * collision/reduce.cl:5-58) with the accumulator list of Bounds
  * (collision/bounds.py:5): out_minmax = {min[lanes], max[lanes]} over n slots of
  * `lanes` scalars (1, 2, 4, 8 or 16; a 3-vector is a 4-lane slot).  One launch.
- * col_sum is the Summer accumulator (collision/summer.py:4-8): out = {sum[lanes]}. */
+ * col_sum is the Summer accumulator (collision/summer.py:4-8): out = {sum[lanes]};
+ * besides COL_F32/COL_F64 it takes the integer codes (sums wrap, exact in any order). */
 size_t col_reduce_scratch_bytes(void);
 int col_bounds(const void* values, uint64_t n, int dtype, uint32_t lanes, void* out_minmax,
                void* scratch, void* stream);

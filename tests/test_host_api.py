@@ -231,3 +231,10 @@ def test_bounds_program():
     assert (r.ngroups, r.group_size) == (8, 16)
     assert SumProgram(CTX, np.dtype('float64')).acc_dtype == np.dtype(('float64', 1))
     assert Summer(CTX, 4, 8, np.dtype('float32')).program.value_dtype == np.dtype('float32')
+    # integer sums (tests/test_summer_py.py:12); min/max stays floating point (its initialisers are +-INFINITY)
+    assert SumProgram(CTX, np.dtype(('uint32', 4))).acc_dtype == np.dtype((('uint32', 4), 1))
+    assert Summer(CTX, 4, 8, np.dtype('int32')).program.value_dtype == np.dtype('int32')
+    with pytest.raises(ValueError):
+        BoundsProgram(CTX, np.dtype(('uint32', 4)))
+    with pytest.raises(ValueError):
+        SumProgram(CTX, np.dtype('uint16'))

@@ -187,6 +187,28 @@ def test_sum(cuda_env, coord_dtype):
     np.testing.assert_allclose(got[:3], values.sum(axis=0)[:3], rtol=1e-5)
 
 
+@pytest.mark.parametrize("size", [100, 1000003])
+@pytest.mark.parametrize("coord_dtype", [("uint32", 4), "int32", ("uint32", 3), "uint64", ("int64", 2)])
+def test_sum_integer(cuda_env, coord_dtype, size):
+    # tests/test_summer_py.py:12 (uint32x4, int32): integer sums wrap, so they are exact in any order
+    from collision_b200.summer import Summer
+    from collision_b200.misc import dtype_sizeof
+    dev, cq = cuda_env
+    cdt = np.dtype(coord_dtype)
+    lanes = dtype_sizeof(cdt) // cdt.base.itemsize
+    rng = np.random.RandomState(5)
+    if size == 100:
+        values = rng.uniform(0, 200, size=(size, lanes)).astype(cdt.base)       # upstream's values
+    else:
+        info = np.iinfo(cdt.base)                                                 # full range: the sum wraps
+        values = rng.randint(info.min, info.max, size=(size, lanes), dtype=cdt.base)
+    out_buf = dev_empty(dtype_sizeof(cdt), fill=0xEE)
+    Summer(dev, 4, 8, cdt).reduce(cq, size, to_dev(values), out_buf).synchronize()
+    got = to_host(out_buf, cdt.base, (lanes,))
+    with np.errstate(over='ignore'):
+        np.testing.assert_equal(got, values.sum(axis=0, dtype=cdt.base))
+
+
 # ----------------------------------------------------------------- offsets
 @pytest.mark.parametrize("vdt,odt", [("uint32", "uint32"), ("uint64", "uint64"), ("uint32", "uint64")])
 def test_offsets(cuda_env, oracle, vdt, odt):
