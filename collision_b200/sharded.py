@@ -27,6 +27,43 @@ def shard_range(n, world, rank):
     return (n * rank) // world, (n * (rank + 1)) // world
 
 
+def rebalance_edges(edges, totals, query_weight=1):
+    """Query-range edges for the NEXT call from the LAST call's per-rank row totals (SURVEY 8(e):
+    "for clustered data repartition by equal pair counts using the gathered counts").
+
+    `edges`: the world+1 sorted positions the last call was split at (edges[0] = 0, edges[-1] = n);
+    `totals`: the rows each rank reported over its range.  The cost of a range is modelled as
+    rows + query_weight * queries, spread evenly inside each old range (piecewise-constant
+    density), and the new edges cut that cost into `world` equal parts.  Pure integer
+    arithmetic on values every rank holds after the all-gather, so all ranks derive the same
+    edges without another exchange; repeated over the frames of a moving scene it converges
+    on the balanced split.  The row list is unaffected: rank-major concatenation of
+    contiguous sorted ranges is the 1-GPU list for ANY edges."""
+    world = len(totals)
+    if len(edges) != world + 1 or any(b > e for b, e in zip(edges, edges[1:])):
+        raise ValueError("edges must be world + 1 non-decreasing positions")
+    lens = [e - b for b, e in zip(edges, edges[1:])]
+    cost = [int(t) + query_weight * l for t, l in zip(totals, lens)]
+    whole = sum(cost)
+    if whole == 0:
+        return list(edges)
+    new = [edges[0]]
+    seg, before = 0, 0                       # current old range and the cost of the ranges before it
+    for j in range(1, world):
+        # smallest position whose cost prefix reaches j/world of the whole:  before + cost[seg]*x/lens[seg] >= whole*j/world
+        while seg < world - 1 and (before + cost[seg]) * world <= whole * j:
+            before += cost[seg]
+            seg += 1
+        if cost[seg] == 0:
+            x = 0
+        else:
+            need = whole * j - before * world            # = (target - before) * world, >= 0
+            x = -((-need * lens[seg]) // (cost[seg] * world))    # ceil
+        new.append(max(new[-1], min(edges[seg] + x, edges[seg + 1])))
+    new.append(edges[-1])
+    return new
+
+
 def exchange_totals(local_total, group=None):
     """all_gather of the per-rank row counts.  `local_total`: 1-element int64 tensor on
     the group's device.  Returns the (world,) int64 tensor of totals (same device);
@@ -75,7 +112,7 @@ class ShardedCollider:
     MODES = ("broadcast_tree", "replicate_build", "gather_inputs")
 
     def __init__(self, ctx, size, ngroups, group_size, coord_dtype=dtype('float32'), group=None, src=0,
-                 mode="broadcast_tree"):
+                 mode="broadcast_tree", balance=False, query_weight=1):
         """mode "broadcast_tree" (north_star): rank `src` sorts, builds and refits; the
         traversal data (68 B per sphere) is broadcast.
         mode "replicate_build": the INPUT (coords + radii, 20 B per sphere) is broadcast
@@ -84,7 +121,11 @@ class ShardedCollider:
         compute for 3.4x less NVLink traffic and no serial rank-0 phase.
         mode "gather_inputs": as "replicate_build", but the scene arrives sharded -- every rank
         owns the spheres [size*r/k, size*(r+1)/k) -- and is all-gathered in place (the same
-        bytes over NVLink, but k host links feed it instead of one)."""
+        bytes over NVLink, but k host links feed it instead of one).
+        balance=True: after every call (with sync_totals) the query ranges of the next call are
+        re-cut by `rebalance_edges` from the all-gathered row totals, so that a clustered scene
+        called frame after frame converges on equal work per rank; the first call uses the
+        equal-queries split.  The rows and their order are the same for any split."""
         if mode not in self.MODES:
             raise ValueError("mode must be one of {}".format(self.MODES))
         self.mode = mode
@@ -94,7 +135,10 @@ class ShardedCollider:
         self.world = dist.get_world_size(group)
         self.rank = dist.get_rank(group)
         self.size = size
-        self.q_begin, self.q_end = shard_range(size, self.world, self.rank)
+        self.balance = balance
+        self.query_weight = query_weight
+        self.edges = [shard_range(size, self.world, r)[0] for r in range(self.world)] + [size]
+        self.q_begin, self.q_end = self.edges[self.rank], self.edges[self.rank + 1]
         self.local_pairs = 0
         self.pair_base = 0
         self.total_pairs = 0
@@ -159,4 +203,7 @@ class ShardedCollider:
             self.local_pairs = t[self.rank]
             self.pair_base = sum(t[:self.rank])
             self.total_pairs = sum(t)
+            if self.balance:    # identical on every rank: same edges, same gathered totals
+                self.edges = rebalance_edges(self.edges, t, self.query_weight)
+                self.q_begin, self.q_end = self.edges[self.rank], self.edges[self.rank + 1]
         return ev

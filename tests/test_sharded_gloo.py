@@ -106,3 +106,111 @@ def test_two_rank_input_gather(tmp_path, n):
     for k in range(world):
         np.testing.assert_equal(np.load(tmp_path / "coords{}.npy".format(k)), c.astype(np.float32))
         np.testing.assert_equal(np.load(tmp_path / "radii{}.npy".format(k)), r.astype(np.float32))
+
+
+# ------------------------------------------------------------------ balanced split
+def test_rebalance_edges_properties():
+    from collision_b200.sharded import rebalance_edges, shard_range
+    rng = np.random.RandomState(7)
+    for world in (1, 2, 4, 8):
+        for n in (1, 9, 1000, (1 << 27) + 3):
+            edges = [shard_range(n, world, r)[0] for r in range(world)] + [n]
+            for trial in range(20):
+                totals = [int(t) for t in rng.randint(0, 1 << 40, size=world) * rng.randint(0, 2, size=world)]
+                totals = [t if e > b else 0 for t, b, e in zip(totals, edges, edges[1:])]   # no queries, no rows
+                for w in (0, 1, 16):
+                    new = rebalance_edges(edges, totals, w)
+                    assert len(new) == world + 1 and new[0] == 0 and new[-1] == n
+                    assert all(a <= b for a, b in zip(new, new[1:]))
+                    # under the piecewise-constant model every new range carries whole/world (+- one query's cost)
+                    cost = [t + w * (e - b) for t, b, e in zip(totals, edges, edges[1:])]
+                    whole = sum(cost)
+                    if whole == 0:
+                        assert new == edges
+                        continue
+
+                    def prefix(x):      # modelled cost of the positions [0, x), as an exact fraction * world
+                        c = 0.0
+                        for k in range(world):
+                            if edges[k + 1] > edges[k]:
+                                c += cost[k] * (min(max(x, edges[k]), edges[k + 1]) - edges[k]) / (edges[k + 1] - edges[k])
+                        return c
+                    per_query = max(cst / max(e - b, 1) for cst, b, e in zip(cost, edges, edges[1:]))
+                    for j in range(1, world):
+                        # the cut sits at the first position whose cost prefix reaches j/world of the whole
+                        assert prefix(new[j]) >= whole * j / world * (1 - 1e-9) - 1e-6
+                        assert prefix(new[j]) - whole * j / world <= per_query * (1 + 1e-9) + 1e-6
+    # the same totals over unequal edges; all-zero ranges keep their positions only if nothing was seen anywhere
+    assert rebalance_edges([0, 50, 100], [100, 0], 0) == [0, 25, 100]
+    assert rebalance_edges([0, 25, 50, 75, 100], [0, 0, 0, 0], 0) == [0, 25, 50, 75, 100]
+    assert rebalance_edges([0, 0, 0, 100], [0, 0, 50], 1) == [0, 34, 67, 100]
+    with pytest.raises(ValueError):
+        rebalance_edges([0, 60, 50, 100], [1, 1, 1])
+    with pytest.raises(ValueError):
+        rebalance_edges([0, 50, 100], [1, 1, 1])
+
+
+def test_rebalance_converges_on_a_skewed_density():
+    """Frame after frame on a fixed scene the per-rank rows approach whole/world."""
+    from collision_b200.sharded import rebalance_edges, shard_range
+    n, world = 1 << 16, 8
+    rng = np.random.RandomState(3)
+    rows = (rng.pareto(3.0, size=n) * 8).astype(np.int64)           # skewed rows per query ...
+    rows[: n // 8] *= 20                                             # ... and one dense region
+    csum = np.concatenate([[0], np.cumsum(rows)])
+    edges = [shard_range(n, world, r)[0] for r in range(world)] + [n]
+    spread = []
+    for frame in range(6):
+        totals = [int(csum[e] - csum[b]) for b, e in zip(edges, edges[1:])]
+        spread.append(max(totals) / (sum(totals) / world))
+        edges = rebalance_edges(edges, totals, 0)
+    assert spread[0] > 3.0           # the equal-queries split is badly skewed here
+    assert spread[-1] < 1.05         # the re-cut split is balanced to 5 %
+    assert max(spread[2:]) < 1.05    # and stays there (it may wobble by a query or two)
+
+
+def _balance_worker(rank, world, port, n, tmpdir):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        import oracle
+        from collision_b200.sharded import exchange_totals, rebalance_edges, shard_range
+        c, r = _skewed_scene(n)
+        res = oracle.collide(c, r)      # every rank builds the identical tree ("replicate_build")
+        edges = [shard_range(n, world, k)[0] for k in range(world)] + [n]
+        log = []
+        for frame in range(3):
+            total, pairs, _ = oracle.traverse(res['nodes'], res['bounds'], q_begin=edges[rank], q_end=edges[rank + 1])
+            totals = exchange_totals(torch.tensor([total], dtype=torch.int64)).tolist()
+            np.save(os.path.join(tmpdir, "pairs{}_{}.npy".format(frame, rank)), pairs)
+            log.append(list(edges) + totals)
+            edges = rebalance_edges(edges, totals, 1)
+        np.save(os.path.join(tmpdir, "log{}.npy".format(rank)), np.array(log))
+    finally:
+        dist.destroy_process_group()
+
+
+def _skewed_scene(n):
+    """Half the spheres packed into a small corner (many overlaps), half spread out."""
+    c, r = G.random_spheres(n)
+    c = c.copy()
+    c[: n // 2, :3] *= 0.2
+    return c, r
+
+
+def test_two_rank_rebalanced_split_keeps_the_list(oracle, tmp_path):
+    n, world = 2000, 2
+    mp.spawn(_balance_worker, args=(world, _free_port(), n, str(tmp_path)), nprocs=world, join=True)
+    c, r = _skewed_scene(n)
+    want = oracle.collide(c, r)
+    logs = [np.load(tmp_path / "log{}.npy".format(k)) for k in range(world)]
+    np.testing.assert_equal(logs[0], logs[1])            # every rank derived the same edges from the same totals
+    for frame in range(3):
+        parts = [np.load(tmp_path / "pairs{}_{}.npy".format(frame, k)) for k in range(world)]
+        # any contiguous split gives the single-rank (sequential reference) list
+        np.testing.assert_equal(np.concatenate(parts), want['pairs'])
+        assert logs[0][frame][world + 1:].sum() == want['total']
+    first, last = logs[0][0][world + 1:], logs[0][-1][world + 1:]
+    assert first.max() / first.sum() > 0.6               # equal-queries split: one rank holds most rows
+    assert last.max() / last.sum() < first.max() / first.sum()
+    assert (logs[0][0][:world + 1] != logs[0][-1][:world + 1]).any()
