@@ -132,6 +132,183 @@ scan_kernel(uint32_t* __restrict__ data, uint64_t n, uint64_t* total_out, unsign
     }
 }
 
+// ---------------------------------------------------------------- large arrays
+// Above COL_SCAN_TWO_PHASE_MIN values the look-back latency of the single-pass kernel costs more
+// than a second read: a persistent grid (every block co-resident, cooperative launch) cuts the
+// array into one contiguous segment per block and runs reduce-then-scan with ONE grid-wide
+// arrival barrier in between.  Phase 1 sums the segment BACK TO FRONT, phase 2 scans it front to
+// back, in place: the part of the segment read last is re-read first, while it still sits in
+// the 126 MB L2, and the scan's stores land on lines it has just read.  HBM traffic is
+// 12 B per value minus the L2 hits of the re-read (8 B algorithmic); no block ever waits on
+// another except at the barrier.
+#ifndef COL_SCAN_TWO_PHASE_MIN
+#define COL_SCAN_TWO_PHASE_MIN (1ull << 24)
+#endif
+#ifndef COL_SCAN_RS_VECS
+#define COL_SCAN_RS_VECS 4
+#endif
+#ifndef COL_SCAN_RS_MAX_CTAS
+#define COL_SCAN_RS_MAX_CTAS 4
+#endif
+constexpr int RS_THREADS = 256;
+constexpr int RS_VECS = COL_SCAN_RS_VECS;                 // uint4 per thread per tile
+constexpr int RS_TILE = RS_THREADS * RS_VECS * 4;         // values per tile
+constexpr int RS_WARP_ITEMS = 32 * RS_VECS * 4;           // contiguous values per warp per tile
+constexpr size_t RS_TOTALS_OFF = 256;                     // scratch: [0] arrival counter, then u64 per block
+
+__global__ void __launch_bounds__(RS_THREADS)
+scan_two_phase_kernel(uint32_t* __restrict__ data, uint64_t n, uint64_t seg_len, uint64_t* total_out,
+                      uint32_t* arrivals, uint64_t* seg_total) {
+    __shared__ uint64_t s_red[RS_THREADS / 32];
+    __shared__ uint64_t s_pre[2];
+    __shared__ uint32_t s_wtot[2][RS_THREADS / 32];
+    const unsigned warp = threadIdx.x >> 5, lane = lane_id();
+    const uint64_t seg_begin = min(n, (uint64_t)blockIdx.x * seg_len);
+    const uint64_t seg_end = min(n, seg_begin + seg_len);
+    const int64_t tiles = (int64_t)((seg_end - seg_begin + RS_TILE - 1) / RS_TILE);
+    // element offset, inside a tile, of this thread's k-th vector (warp-major, as in scan_kernel)
+    const uint32_t my_off = warp * RS_WARP_ITEMS + lane * 4;
+
+    // ---- phase 1: segment total, back to front
+    uint64_t acc = 0;
+    for (int64_t t = tiles - 1; t >= 0; t--) {
+        const uint64_t base = seg_begin + (uint64_t)t * RS_TILE;
+        if (base + RS_TILE <= seg_end) {
+            uint4 v[RS_VECS];
+#pragma unroll
+            for (int k = 0; k < RS_VECS; k++) v[k] = *reinterpret_cast<const uint4*>(data + base + my_off + k * 128);
+#pragma unroll
+            for (int k = 0; k < RS_VECS; k++) acc += (uint64_t)v[k].x + v[k].y + v[k].z + v[k].w;
+        } else {
+            for (uint64_t e = base + threadIdx.x; e < seg_end; e += RS_THREADS) acc += data[e];
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    if (lane == 0) s_red[warp] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint64_t t = 0;
+#pragma unroll
+        for (int w = 0; w < RS_THREADS / 32; w++) t += s_red[w];
+        st_relaxed_u64(seg_total + blockIdx.x, t);
+        __threadfence();
+        atomicAdd(arrivals, 1u);
+        while (ld_acquire_u32(arrivals) < gridDim.x) __nanosleep(64);
+    }
+    __syncthreads();
+
+    // ---- prefix of the segment totals before mine (and the grand total)
+    {
+        uint64_t before = 0, all = 0;
+        for (unsigned b = threadIdx.x; b < gridDim.x; b += RS_THREADS) {
+            const uint64_t t = ld_relaxed_u64(seg_total + b);
+            all += t;
+            if (b < blockIdx.x) before += t;
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            before += __shfl_xor_sync(0xffffffffu, before, o);
+            all += __shfl_xor_sync(0xffffffffu, all, o);
+        }
+        __syncthreads();     // s_red is reused
+        if (lane == 0) s_red[warp] = before;
+        if (blockIdx.x == 0 && total_out) {      // block 0 alone needs the grand total
+            __shared__ uint64_t s_all[RS_THREADS / 32];
+            if (lane == 0) s_all[warp] = all;
+            __syncthreads();
+            if (threadIdx.x == 0) {
+                uint64_t t = 0;
+#pragma unroll
+                for (int w = 0; w < RS_THREADS / 32; w++) t += s_all[w];
+                *total_out = t;
+            }
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            uint64_t t = 0;
+#pragma unroll
+            for (int w = 0; w < RS_THREADS / 32; w++) t += s_red[w];
+            s_pre[0] = t;
+        }
+        __syncthreads();
+    }
+
+    // ---- phase 2: exclusive scan of the segment, front to back, in place (mod 2^32)
+    uint32_t carry = (uint32_t)s_pre[0];
+    for (int64_t t = 0; t < tiles; t++) {
+        const uint64_t base = seg_begin + (uint64_t)t * RS_TILE;
+        const bool full = base + RS_TILE <= seg_end;
+        uint4 v[RS_VECS];
+#pragma unroll
+        for (int k = 0; k < RS_VECS; k++) {
+            const uint64_t e = base + my_off + k * 128;
+            if (full) {
+                v[k] = *reinterpret_cast<const uint4*>(data + e);
+            } else {
+                v[k].x = e + 0 < seg_end ? data[e + 0] : 0u;
+                v[k].y = e + 1 < seg_end ? data[e + 1] : 0u;
+                v[k].z = e + 2 < seg_end ? data[e + 2] : 0u;
+                v[k].w = e + 3 < seg_end ? data[e + 3] : 0u;
+            }
+        }
+        uint32_t excl[RS_VECS];
+        uint32_t row_base = 0;
+#pragma unroll
+        for (int k = 0; k < RS_VECS; k++) {
+            const uint32_t sum = v[k].x + v[k].y + v[k].z + v[k].w;
+            uint32_t inc = sum;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t up = __shfl_up_sync(0xffffffffu, inc, o);
+                if (lane >= o) inc += up;
+            }
+            excl[k] = row_base + inc - sum;
+            row_base += __shfl_sync(0xffffffffu, inc, 31);
+        }
+        uint32_t* wt = s_wtot[t & 1];            // double-buffered: one barrier per tile
+        if (lane == 0) wt[warp] = row_base;
+        __syncthreads();
+        uint32_t warp_prefix = 0, tile_total = 0;
+#pragma unroll
+        for (int w = 0; w < RS_THREADS / 32; w++) {
+            const uint32_t x = wt[w];
+            if (w < (int)warp) warp_prefix += x;
+            tile_total += x;
+        }
+        const uint32_t b0 = carry + warp_prefix;
+#pragma unroll
+        for (int k = 0; k < RS_VECS; k++) {
+            const uint64_t e = base + my_off + k * 128;
+            uint4 o;
+            o.x = b0 + excl[k];
+            o.y = o.x + v[k].x;
+            o.z = o.y + v[k].y;
+            o.w = o.z + v[k].z;
+            if (full) {
+                *reinterpret_cast<uint4*>(data + e) = o;
+            } else {
+                if (e + 0 < seg_end) data[e + 0] = o.x;
+                if (e + 1 < seg_end) data[e + 1] = o.y;
+                if (e + 2 < seg_end) data[e + 2] = o.z;
+                if (e + 3 < seg_end) data[e + 3] = o.w;
+            }
+        }
+        carry += tile_total;
+    }
+}
+
+// blocks of the persistent grid: what the device can hold at once (0 = query failed)
+int two_phase_grid() {
+    int dev = 0, sms = 0, per_sm = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return 0;
+    if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) return 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, scan_two_phase_kernel, RS_THREADS, 0) != cudaSuccess)
+        return 0;
+    if (per_sm > COL_SCAN_RS_MAX_CTAS) per_sm = COL_SCAN_RS_MAX_CTAS;
+    return sms * per_sm;
+}
+
 }  // namespace
 
 COL_API size_t col_scan_scratch_bytes(uint64_t n) {
@@ -148,6 +325,22 @@ COL_API int col_exclusive_scan_u32(uint32_t* data, uint64_t n, uint64_t* total_o
     }
     const uint64_t tiles = (n + SCAN_TILE - 1) / SCAN_TILE;
     if (tiles > 0x7fffffffull) return COL_ERR_TOO_LARGE;
+    if (n >= COL_SCAN_TWO_PHASE_MIN && (reinterpret_cast<uintptr_t>(data) & 15u) == 0) {
+        const int grid = two_phase_grid();
+        // the per-block totals take the place of the tile status words (far fewer blocks than tiles here)
+        if (grid > 0 && RS_TOTALS_OFF + (size_t)grid * sizeof(uint64_t) <= col_scan_scratch_bytes(n)) {
+            COL_CUDA(cudaMemsetAsync(scratch, 0, sizeof(uint32_t), s));
+            uint32_t* arrivals = reinterpret_cast<uint32_t*>(scratch);
+            uint64_t* seg_total = reinterpret_cast<uint64_t*>(reinterpret_cast<char*>(scratch) + RS_TOTALS_OFF);
+            uint64_t seg_len = (n + grid - 1) / grid;
+            seg_len = (seg_len + RS_TILE - 1) / RS_TILE * RS_TILE;     // whole tiles: segments stay 16-byte aligned
+            void* args[] = {&data, &n, &seg_len, &total_out, &arrivals, &seg_total};
+            // cooperative: the launch fails instead of hanging if the grid could not be co-resident
+            COL_CUDA(cudaLaunchCooperativeKernel((const void*)scan_two_phase_kernel, dim3((unsigned)grid),
+                                                 dim3(RS_THREADS), args, 0, s));
+            return 0;
+        }
+    }
     COL_CUDA(cudaMemsetAsync(scratch, 0, col_scan_scratch_bytes(n), s));
     unsigned* ticket = reinterpret_cast<unsigned*>(scratch);
     uint64_t* status = reinterpret_cast<uint64_t*>(reinterpret_cast<char*>(scratch) + SCAN_STATUS_OFF);

@@ -38,6 +38,35 @@ def test_prefix_sum(cuda_env, oracle, size, group_size):
         np.testing.assert_equal(to_host(buf, 'uint32', (size,)), oracle.exclusive_scan(values))
 
 
+@pytest.mark.parametrize("size", [1 << 24, (1 << 24) + 4097, (1 << 25) + 1, 3 * (1 << 23) + 777])
+@pytest.mark.parametrize("misaligned", [False, True])
+def test_scan_large(cuda_env, size, misaligned):
+    """From 2^24 values on the scan runs as a persistent reduce-then-scan grid (one segment per block):
+    ragged last segment / last tile, wrapping values, the u64 grand total, and the fall-back to the
+    single-pass kernel when the buffer is not 16-byte aligned."""
+    import torch
+    from collision_b200 import _lib
+    dev, cq = cuda_env
+    L, P, S = _lib.lib(), _lib.ptr, cq.cuda_stream
+    g = torch.Generator(device=dev).manual_seed(size & 0xFFFF)
+    wide = torch.randint(0, 1 << 32, (size,), dtype=torch.int64, device=dev, generator=g)
+    store = torch.empty(size + 1, dtype=torch.int32, device=dev)
+    data = store[1:] if misaligned else store[:size]
+    data.copy_(wide.to(torch.int32))
+    want = torch.cumsum(wide, 0)
+    scratch = _lib.alloc_bytes(dev, L.col_scan_scratch_bytes(size))
+    tot = torch.zeros(1, dtype=torch.int64, device=dev)
+    cq.wait_stream(torch.cuda.current_stream(dev))
+    for _ in range(2):      # the scratch is reusable as it is left
+        data.copy_(wide.to(torch.int32))
+        cq.wait_stream(torch.cuda.current_stream(dev))
+        assert L.col_exclusive_scan_u32(data.data_ptr(), size, P(tot), P(scratch), S) == 0
+        cq.synchronize()
+        assert int(tot.item()) == int(want[-1].item())
+        assert data[0].item() == 0
+        assert torch.equal(data[1:].to(torch.int64) & 0xFFFFFFFF, want[:-1] & 0xFFFFFFFF)
+
+
 def test_scanner_resize(cuda_env, oracle):
     # tests/test_scan_py.py:67-92
     from collision_b200.scan import PrefixScanner
