@@ -1,4 +1,5 @@
-// scan.cu -- single-pass exclusive prefix sum of uint32 (decoupled look-back).
+// scan.cu -- exclusive prefix sum of uint32: single pass with decoupled look-back, and from 2^24
+// values on a persistent chunked grid that re-reads each tile from L2 (second half of the file).
 //
 // Replaces PrefixScanner.prefix_sum (collision/scan.py:75-112): the reference
 // runs 2*levels+1 launches (local_scan per level, then block_scan per level:
@@ -133,187 +134,179 @@ scan_kernel(uint32_t* __restrict__ data, uint64_t n, uint64_t* total_out, unsign
 }
 
 // ---------------------------------------------------------------- large arrays
-// Above COL_SCAN_TWO_PHASE_MIN values the look-back latency of the single-pass kernel costs more
-// than a second read: a persistent grid (every block co-resident, cooperative launch) cuts the
-// array into one contiguous segment per block and runs reduce-then-scan with ONE grid-wide
-// arrival barrier in between.  Phase 1 sums the segment BACK TO FRONT, phase 2 scans it front to
-// back, in place: the part of the segment read last is re-read first, while it still sits in
-// the 126 MB L2, and the scan's stores land on lines it has just read.  HBM traffic is
-// 12 B per value minus the L2 hits of the re-read (8 B algorithmic); no block ever waits on
-// another except at the barrier.
-#ifndef COL_SCAN_TWO_PHASE_MIN
-#define COL_SCAN_TWO_PHASE_MIN (1ull << 24)
+// From COL_SCAN_LAGGED_MIN values on, the look-back latency of the single-pass kernel costs more
+// than it saves (measured: half of copy speed).  A persistent grid (every block co-resident:
+// cooperative launch) cuts the array into CHUNKS of one tile per block, and every block alternates:
+// sum my tile of chunk c and publish the sum (phase 1), then scan my tile of chunk c - LAG in
+// place (phase 2).  By then every block's sum of that chunk has long been published -- there is
+// no chain of look-backs: a block adds the `grid` sums of the chunk itself, all loads in flight
+// at once -- and the tile is still in L2 (LAG + 1 chunks, ~45 MB of the 126, are live), so the
+// second read costs no HBM traffic: 8 B per value.  A sum is a 64-bit word {valid:1, sum:63};
+// the words are zeroed before the launch.  Waits only ever point at lower chunks, and phase 1
+// never waits, so the grid cannot deadlock.  Measured alternatives (profiles/r1g_scan_variants*.txt):
+// LAG 1 (blocks wait on stragglers, 1.5x slower), LAG 3-4 and L2 prefetch of later chunks (the
+// live set outgrows what L2 keeps), 16 KB tiles x 4 blocks per SM (-3 %), issuing the re-read before
+// phase 1 (registers), and plain reduce-then-scan over one segment per block (12 B per value).
+#ifndef COL_SCAN_LAGGED_MIN
+#define COL_SCAN_LAGGED_MIN (1ull << 24)
 #endif
-#ifndef COL_SCAN_RS_VECS
-#define COL_SCAN_RS_VECS 4
+#ifndef COL_SCAN_LAGGED
+#define COL_SCAN_LAGGED 1
 #endif
-#ifndef COL_SCAN_RS_MAX_CTAS
-#define COL_SCAN_RS_MAX_CTAS 4
+#ifndef COL_SCAN_LG_VECS
+#define COL_SCAN_LG_VECS 8
 #endif
-constexpr int RS_THREADS = 256;
-constexpr int RS_VECS = COL_SCAN_RS_VECS;                 // uint4 per thread per tile
-constexpr int RS_TILE = RS_THREADS * RS_VECS * 4;         // values per tile
-constexpr int RS_WARP_ITEMS = 32 * RS_VECS * 4;           // contiguous values per warp per tile
-constexpr size_t RS_TOTALS_OFF = 256;                     // scratch: [0] arrival counter, then u64 per block
+#ifndef COL_SCAN_LG_LAG
+#define COL_SCAN_LG_LAG 2
+#endif
+#ifndef COL_SCAN_LG_CTAS
+#define COL_SCAN_LG_CTAS 3            // blocks per SM (80 registers per thread)
+#endif
+constexpr int LG_THREADS = 256;
+constexpr int LG_VECS = COL_SCAN_LG_VECS;         // uint4 per thread per tile
+constexpr int LG_TILE = LG_THREADS * LG_VECS * 4; // 8192 values
+constexpr int LG_WARP_ITEMS = 32 * LG_VECS * 4;   // contiguous values per warp
+constexpr int LG_LAG = COL_SCAN_LG_LAG;
+constexpr int LG_MIN_TILE = 2048;                 // scratch is sized for tiles at least this long
+constexpr int LG_MAX_GRID = 4096;                 // ... and for grids up to this many blocks
+constexpr uint64_t LG_VALID = 1ull << 63;
 
-__global__ void __launch_bounds__(RS_THREADS)
-scan_two_phase_kernel(uint32_t* __restrict__ data, uint64_t n, uint64_t seg_len, uint64_t* total_out,
-                      uint32_t* arrivals, uint64_t* seg_total) {
-    __shared__ uint64_t s_red[RS_THREADS / 32];
-    __shared__ uint64_t s_pre[2];
-    __shared__ uint32_t s_wtot[2][RS_THREADS / 32];
+__global__ void __launch_bounds__(LG_THREADS, COL_SCAN_LG_CTAS)
+scan_lagged_kernel(uint32_t* __restrict__ data, uint64_t n, uint32_t chunks, uint64_t* total_out, uint64_t* sums) {
+    __shared__ uint64_t s_red[2][LG_THREADS / 32];
+    __shared__ uint64_t s_before[LG_THREADS / 32], s_all[LG_THREADS / 32];
+    __shared__ uint32_t s_wtot[LG_THREADS / 32];
     const unsigned warp = threadIdx.x >> 5, lane = lane_id();
-    const uint64_t seg_begin = min(n, (uint64_t)blockIdx.x * seg_len);
-    const uint64_t seg_end = min(n, seg_begin + seg_len);
-    const int64_t tiles = (int64_t)((seg_end - seg_begin + RS_TILE - 1) / RS_TILE);
-    // element offset, inside a tile, of this thread's k-th vector (warp-major, as in scan_kernel)
-    const uint32_t my_off = warp * RS_WARP_ITEMS + lane * 4;
+    const unsigned G = gridDim.x, b = blockIdx.x;
+    const uint32_t my_off = warp * LG_WARP_ITEMS + lane * 4;
+    uint64_t carry = 0;                            // sum of all chunks before the one being scanned
 
-    // ---- phase 1: segment total, back to front
-    uint64_t acc = 0;
-    for (int64_t t = tiles - 1; t >= 0; t--) {
-        const uint64_t base = seg_begin + (uint64_t)t * RS_TILE;
-        if (base + RS_TILE <= seg_end) {
-            uint4 v[RS_VECS];
+    for (uint32_t c = 0; c < chunks + LG_LAG; c++) {
+        // ---- phase 1: sum of my tile of chunk c
+        if (c < chunks) {
+            const uint64_t base = ((uint64_t)c * G + b) * LG_TILE;
+            uint64_t acc = 0;
+            if (base + LG_TILE <= n) {
+                uint4 a[LG_VECS];
 #pragma unroll
-            for (int k = 0; k < RS_VECS; k++) v[k] = *reinterpret_cast<const uint4*>(data + base + my_off + k * 128);
+                for (int k = 0; k < LG_VECS; k++) a[k] = *reinterpret_cast<const uint4*>(data + base + my_off + k * 128);
 #pragma unroll
-            for (int k = 0; k < RS_VECS; k++) acc += (uint64_t)v[k].x + v[k].y + v[k].z + v[k].w;
-        } else {
-            for (uint64_t e = base + threadIdx.x; e < seg_end; e += RS_THREADS) acc += data[e];
-        }
-    }
+                for (int k = 0; k < LG_VECS; k++) acc += (uint64_t)a[k].x + a[k].y + a[k].z + a[k].w;
+            } else {
+                for (uint64_t e = base + threadIdx.x; e < n; e += LG_THREADS) acc += data[e];
+            }
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
-    if (lane == 0) s_red[warp] = acc;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        uint64_t t = 0;
-#pragma unroll
-        for (int w = 0; w < RS_THREADS / 32; w++) t += s_red[w];
-        st_relaxed_u64(seg_total + blockIdx.x, t);
-        __threadfence();
-        atomicAdd(arrivals, 1u);
-        while (ld_acquire_u32(arrivals) < gridDim.x) __nanosleep(64);
-    }
-    __syncthreads();
-
-    // ---- prefix of the segment totals before mine (and the grand total)
-    {
-        uint64_t before = 0, all = 0;
-        for (unsigned b = threadIdx.x; b < gridDim.x; b += RS_THREADS) {
-            const uint64_t t = ld_relaxed_u64(seg_total + b);
-            all += t;
-            if (b < blockIdx.x) before += t;
-        }
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            before += __shfl_xor_sync(0xffffffffu, before, o);
-            all += __shfl_xor_sync(0xffffffffu, all, o);
-        }
-        __syncthreads();     // s_red is reused
-        if (lane == 0) s_red[warp] = before;
-        if (blockIdx.x == 0 && total_out) {      // block 0 alone needs the grand total
-            __shared__ uint64_t s_all[RS_THREADS / 32];
-            if (lane == 0) s_all[warp] = all;
+            for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+            if (lane == 0) s_red[c & 1][warp] = acc;
             __syncthreads();
             if (threadIdx.x == 0) {
                 uint64_t t = 0;
 #pragma unroll
-                for (int w = 0; w < RS_THREADS / 32; w++) t += s_all[w];
-                *total_out = t;
+                for (int w = 0; w < LG_THREADS / 32; w++) t += s_red[c & 1][w];
+                st_relaxed_u64(sums + (uint64_t)c * G + b, LG_VALID | t);
             }
         }
-        __syncthreads();
-        if (threadIdx.x == 0) {
-            uint64_t t = 0;
+        // ---- phase 2: scan of my tile of chunk c - LAG
+        if (c >= LG_LAG) {
+            const uint32_t cc = c - LG_LAG;
+            const uint64_t base = ((uint64_t)cc * G + b) * LG_TILE;
+            const bool full = base + LG_TILE <= n;
+            uint4 v[LG_VECS];
 #pragma unroll
-            for (int w = 0; w < RS_THREADS / 32; w++) t += s_red[w];
-            s_pre[0] = t;
+            for (int k = 0; k < LG_VECS; k++) {       // (L2 hits) issued before the sums are waited for
+                const uint64_t e = base + my_off + k * 128;
+                if (full) {
+                    v[k] = *reinterpret_cast<const uint4*>(data + e);
+                } else {
+                    v[k].x = e + 0 < n ? data[e + 0] : 0u;
+                    v[k].y = e + 1 < n ? data[e + 1] : 0u;
+                    v[k].z = e + 2 < n ? data[e + 2] : 0u;
+                    v[k].w = e + 3 < n ? data[e + 3] : 0u;
+                }
+            }
+            uint64_t before = 0, all = 0;
+            for (unsigned i = threadIdx.x; i < G; i += LG_THREADS) {
+                const uint64_t* w = sums + (uint64_t)cc * G + i;
+                uint64_t t = ld_relaxed_u64(w);
+                while (!(t & LG_VALID)) { __nanosleep(32); t = ld_relaxed_u64(w); }
+                t &= ~LG_VALID;
+                all += t;
+                if (i < b) before += t;
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                before += __shfl_xor_sync(0xffffffffu, before, o);
+                all += __shfl_xor_sync(0xffffffffu, all, o);
+            }
+            if (lane == 0) { s_before[warp] = before; s_all[warp] = all; }
+            // per-row warp scans of the tile meanwhile (mod 2^32)
+            uint32_t excl[LG_VECS];
+            uint32_t row_base = 0;
+#pragma unroll
+            for (int k = 0; k < LG_VECS; k++) {
+                const uint32_t sum = v[k].x + v[k].y + v[k].z + v[k].w;
+                uint32_t inc = sum;
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) {
+                    const uint32_t up = __shfl_up_sync(0xffffffffu, inc, o);
+                    if (lane >= o) inc += up;
+                }
+                excl[k] = row_base + inc - sum;
+                row_base += __shfl_sync(0xffffffffu, inc, 31);
+            }
+            if (lane == 0) s_wtot[warp] = row_base;
+            __syncthreads();
+            uint64_t bsum = 0, asum = 0;
+            uint32_t warp_prefix = 0;
+#pragma unroll
+            for (int w = 0; w < LG_THREADS / 32; w++) {
+                bsum += s_before[w];
+                asum += s_all[w];
+                if (w < (int)warp) warp_prefix += s_wtot[w];
+            }
+            const uint32_t b0 = (uint32_t)(carry + bsum) + warp_prefix;
+            carry += asum;
+#pragma unroll
+            for (int k = 0; k < LG_VECS; k++) {
+                const uint64_t e = base + my_off + k * 128;
+                uint4 o;
+                o.x = b0 + excl[k];
+                o.y = o.x + v[k].x;
+                o.z = o.y + v[k].y;
+                o.w = o.z + v[k].z;
+                if (full) {
+                    *reinterpret_cast<uint4*>(data + e) = o;
+                } else {
+                    if (e + 0 < n) data[e + 0] = o.x;
+                    if (e + 1 < n) data[e + 1] = o.y;
+                    if (e + 2 < n) data[e + 2] = o.z;
+                    if (e + 3 < n) data[e + 3] = o.w;
+                }
+            }
+            __syncthreads();     // s_before / s_all / s_wtot are rewritten by the next round
         }
-        __syncthreads();
     }
-
-    // ---- phase 2: exclusive scan of the segment, front to back, in place (mod 2^32)
-    uint32_t carry = (uint32_t)s_pre[0];
-    for (int64_t t = 0; t < tiles; t++) {
-        const uint64_t base = seg_begin + (uint64_t)t * RS_TILE;
-        const bool full = base + RS_TILE <= seg_end;
-        uint4 v[RS_VECS];
-#pragma unroll
-        for (int k = 0; k < RS_VECS; k++) {
-            const uint64_t e = base + my_off + k * 128;
-            if (full) {
-                v[k] = *reinterpret_cast<const uint4*>(data + e);
-            } else {
-                v[k].x = e + 0 < seg_end ? data[e + 0] : 0u;
-                v[k].y = e + 1 < seg_end ? data[e + 1] : 0u;
-                v[k].z = e + 2 < seg_end ? data[e + 2] : 0u;
-                v[k].w = e + 3 < seg_end ? data[e + 3] : 0u;
-            }
-        }
-        uint32_t excl[RS_VECS];
-        uint32_t row_base = 0;
-#pragma unroll
-        for (int k = 0; k < RS_VECS; k++) {
-            const uint32_t sum = v[k].x + v[k].y + v[k].z + v[k].w;
-            uint32_t inc = sum;
-#pragma unroll
-            for (int o = 1; o < 32; o <<= 1) {
-                const uint32_t up = __shfl_up_sync(0xffffffffu, inc, o);
-                if (lane >= o) inc += up;
-            }
-            excl[k] = row_base + inc - sum;
-            row_base += __shfl_sync(0xffffffffu, inc, 31);
-        }
-        uint32_t* wt = s_wtot[t & 1];            // double-buffered: one barrier per tile
-        if (lane == 0) wt[warp] = row_base;
-        __syncthreads();
-        uint32_t warp_prefix = 0, tile_total = 0;
-#pragma unroll
-        for (int w = 0; w < RS_THREADS / 32; w++) {
-            const uint32_t x = wt[w];
-            if (w < (int)warp) warp_prefix += x;
-            tile_total += x;
-        }
-        const uint32_t b0 = carry + warp_prefix;
-#pragma unroll
-        for (int k = 0; k < RS_VECS; k++) {
-            const uint64_t e = base + my_off + k * 128;
-            uint4 o;
-            o.x = b0 + excl[k];
-            o.y = o.x + v[k].x;
-            o.z = o.y + v[k].y;
-            o.w = o.z + v[k].z;
-            if (full) {
-                *reinterpret_cast<uint4*>(data + e) = o;
-            } else {
-                if (e + 0 < seg_end) data[e + 0] = o.x;
-                if (e + 1 < seg_end) data[e + 1] = o.y;
-                if (e + 2 < seg_end) data[e + 2] = o.z;
-                if (e + 3 < seg_end) data[e + 3] = o.w;
-            }
-        }
-        carry += tile_total;
-    }
+    if (b == 0 && threadIdx.x == 0 && total_out) *total_out = carry;
 }
 
-// blocks of the persistent grid: what the device can hold at once (0 = query failed)
-int two_phase_grid() {
+int lagged_grid() {
     int dev = 0, sms = 0, per_sm = 0;
     if (cudaGetDevice(&dev) != cudaSuccess) return 0;
     if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) return 0;
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, scan_two_phase_kernel, RS_THREADS, 0) != cudaSuccess)
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, scan_lagged_kernel, LG_THREADS, 0) != cudaSuccess)
         return 0;
-    if (per_sm > COL_SCAN_RS_MAX_CTAS) per_sm = COL_SCAN_RS_MAX_CTAS;
-    return sms * per_sm;
+    if (per_sm > COL_SCAN_LG_CTAS) per_sm = COL_SCAN_LG_CTAS;
+    const int g = sms * per_sm;
+    return g > LG_MAX_GRID ? LG_MAX_GRID : g;
 }
 
 }  // namespace
 
 COL_API size_t col_scan_scratch_bytes(uint64_t n) {
-    const uint64_t tiles = (n + SCAN_TILE - 1) / SCAN_TILE;
-    return SCAN_STATUS_OFF + (size_t)(tiles ? tiles : 1) * sizeof(uint64_t);
+    // one 64-bit word per tile of whichever kernel runs (the shortest tiles are the chunked kernel's, which
+    // also rounds the tile count up to whole chunks of at most LG_MAX_GRID tiles)
+    static_assert(LG_TILE >= LG_MIN_TILE && SCAN_TILE >= LG_MIN_TILE, "scratch");
+    return SCAN_STATUS_OFF + (size_t)(n / LG_MIN_TILE + 1 + LG_MAX_GRID) * sizeof(uint64_t);
 }
 
 COL_API int col_exclusive_scan_u32(uint32_t* data, uint64_t n, uint64_t* total_out, void* scratch, void* stream) {
@@ -325,23 +318,21 @@ COL_API int col_exclusive_scan_u32(uint32_t* data, uint64_t n, uint64_t* total_o
     }
     const uint64_t tiles = (n + SCAN_TILE - 1) / SCAN_TILE;
     if (tiles > 0x7fffffffull) return COL_ERR_TOO_LARGE;
-    if (n >= COL_SCAN_TWO_PHASE_MIN && (reinterpret_cast<uintptr_t>(data) & 15u) == 0) {
-        const int grid = two_phase_grid();
-        // the per-block totals take the place of the tile status words (far fewer blocks than tiles here)
-        if (grid > 0 && RS_TOTALS_OFF + (size_t)grid * sizeof(uint64_t) <= col_scan_scratch_bytes(n)) {
-            COL_CUDA(cudaMemsetAsync(scratch, 0, sizeof(uint32_t), s));
-            uint32_t* arrivals = reinterpret_cast<uint32_t*>(scratch);
-            uint64_t* seg_total = reinterpret_cast<uint64_t*>(reinterpret_cast<char*>(scratch) + RS_TOTALS_OFF);
-            uint64_t seg_len = (n + grid - 1) / grid;
-            seg_len = (seg_len + RS_TILE - 1) / RS_TILE * RS_TILE;     // whole tiles: segments stay 16-byte aligned
-            void* args[] = {&data, &n, &seg_len, &total_out, &arrivals, &seg_total};
+    if (COL_SCAN_LAGGED && n >= COL_SCAN_LAGGED_MIN && (reinterpret_cast<uintptr_t>(data) & 15u) == 0) {
+        const int grid = lagged_grid();
+        if (grid > 0) {
+            const uint64_t per_chunk = (uint64_t)grid * LG_TILE;
+            uint32_t chunks = (uint32_t)((n + per_chunk - 1) / per_chunk);
+            uint64_t* sums = reinterpret_cast<uint64_t*>(reinterpret_cast<char*>(scratch) + SCAN_STATUS_OFF);
+            COL_CUDA(cudaMemsetAsync(sums, 0, (size_t)chunks * grid * sizeof(uint64_t), s));
+            void* args[] = {&data, &n, &chunks, &total_out, &sums};
             // cooperative: the launch fails instead of hanging if the grid could not be co-resident
-            COL_CUDA(cudaLaunchCooperativeKernel((const void*)scan_two_phase_kernel, dim3((unsigned)grid),
-                                                 dim3(RS_THREADS), args, 0, s));
+            COL_CUDA(cudaLaunchCooperativeKernel((const void*)scan_lagged_kernel, dim3((unsigned)grid),
+                                                 dim3(LG_THREADS), args, 0, s));
             return 0;
         }
     }
-    COL_CUDA(cudaMemsetAsync(scratch, 0, col_scan_scratch_bytes(n), s));
+    COL_CUDA(cudaMemsetAsync(scratch, 0, SCAN_STATUS_OFF + (size_t)tiles * sizeof(uint64_t), s));
     unsigned* ticket = reinterpret_cast<unsigned*>(scratch);
     uint64_t* status = reinterpret_cast<uint64_t*>(reinterpret_cast<char*>(scratch) + SCAN_STATUS_OFF);
     scan_kernel<<<(unsigned)tiles, SCAN_THREADS, 0, s>>>(data, n, total_out, ticket, status);

@@ -41,9 +41,9 @@ def test_prefix_sum(cuda_env, oracle, size, group_size):
 @pytest.mark.parametrize("size", [1 << 24, (1 << 24) + 4097, (1 << 25) + 1, 3 * (1 << 23) + 777])
 @pytest.mark.parametrize("misaligned", [False, True])
 def test_scan_large(cuda_env, size, misaligned):
-    """From 2^24 values on the scan runs as a persistent reduce-then-scan grid (one segment per block):
-    ragged last segment / last tile, wrapping values, the u64 grand total, and the fall-back to the
-    single-pass kernel when the buffer is not 16-byte aligned."""
+    """From 2^24 values on the scan runs as a persistent chunked grid (sum a tile, scan it two chunks
+    later out of L2): ragged last chunk / last tile, wrapping values, the u64 grand total, and the
+    fall-back to the single-pass kernel when the buffer is not 16-byte aligned."""
     import torch
     from collision_b200 import _lib
     dev, cq = cuda_env
@@ -65,6 +65,34 @@ def test_scan_large(cuda_env, size, misaligned):
         assert int(tot.item()) == int(want[-1].item())
         assert data[0].item() == 0
         assert torch.equal(data[1:].to(torch.int64) & 0xFFFFFFFF, want[:-1] & 0xFFFFFFFF)
+
+
+def test_scan_large_in_a_cuda_graph(cuda_env):
+    """The large-array scan is a cooperative launch; it must capture into a CUDA graph and replay
+    (Collider(graph=True) at 2^24 spheres and more goes through it)."""
+    import torch
+    from collision_b200 import _lib
+    dev, cq = cuda_env
+    L, P = _lib.lib(), _lib.ptr
+    size = (1 << 24) + 5000
+    g = torch.Generator(device=dev).manual_seed(11)
+    src = torch.randint(0, 1000, (size,), dtype=torch.int32, device=dev, generator=g)
+    want = torch.cumsum(src.to(torch.int64), 0)
+    data = torch.empty_like(src)
+    scratch = _lib.alloc_bytes(dev, L.col_scan_scratch_bytes(size))
+    tot = torch.zeros(1, dtype=torch.int64, device=dev)
+    torch.cuda.synchronize(dev)
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph, stream=cq):
+        data.copy_(src)
+        assert L.col_exclusive_scan_u32(P(data), size, P(tot), P(scratch), torch.cuda.current_stream(dev).cuda_stream) == 0
+    for _ in range(2):
+        data.zero_()
+        tot.zero_()
+        graph.replay()
+        torch.cuda.synchronize(dev)
+        assert int(tot.item()) == int(want[-1].item())
+        assert data[0].item() == 0 and torch.equal(data[1:].to(torch.int64) & 0xFFFFFFFF, want[:-1] & 0xFFFFFFFF)
 
 
 def test_scanner_resize(cuda_env, oracle):
