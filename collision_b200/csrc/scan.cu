@@ -1,4 +1,4 @@
-// scan.cu -- exclusive prefix sum of uint32: single pass with decoupled look-back, and from 2^24
+// scan.cu -- exclusive prefix sum of uint32: single pass with decoupled look-back, and from 2^23
 // values on a persistent chunked grid that re-reads each tile from L2 (second half of the file).
 //
 // Replaces PrefixScanner.prefix_sum (collision/scan.py:75-112): the reference
@@ -148,7 +148,7 @@ scan_kernel(uint32_t* __restrict__ data, uint64_t n, uint64_t* total_out, unsign
 // live set outgrows what L2 keeps), 16 KB tiles x 4 blocks per SM (-3 %), issuing the re-read before
 // phase 1 (registers), and plain reduce-then-scan over one segment per block (12 B per value).
 #ifndef COL_SCAN_LAGGED_MIN
-#define COL_SCAN_LAGGED_MIN (1ull << 24)
+#define COL_SCAN_LAGGED_MIN (1ull << 23)   // measured crossover (profiles/r1g_scan_threshold.txt)
 #endif
 #ifndef COL_SCAN_LAGGED
 #define COL_SCAN_LAGGED 1

@@ -38,10 +38,10 @@ def test_prefix_sum(cuda_env, oracle, size, group_size):
         np.testing.assert_equal(to_host(buf, 'uint32', (size,)), oracle.exclusive_scan(values))
 
 
-@pytest.mark.parametrize("size", [1 << 24, (1 << 24) + 4097, (1 << 25) + 1, 3 * (1 << 23) + 777])
+@pytest.mark.parametrize("size", [1 << 23, (1 << 23) + 3, (1 << 24) + 4097, (1 << 25) + 1, 3 * (1 << 23) + 777])
 @pytest.mark.parametrize("misaligned", [False, True])
 def test_scan_large(cuda_env, size, misaligned):
-    """From 2^24 values on the scan runs as a persistent chunked grid (sum a tile, scan it two chunks
+    """From 2^23 values on the scan runs as a persistent chunked grid (sum a tile, scan it two chunks
     later out of L2): ragged last chunk / last tile, wrapping values, the u64 grand total, and the
     fall-back to the single-pass kernel when the buffer is not 16-byte aligned."""
     import torch
