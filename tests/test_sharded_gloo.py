@@ -169,13 +169,71 @@ def test_rebalance_converges_on_a_skewed_density():
     assert max(spread[2:]) < 1.05    # and stays there (it may wobble by a query or two)
 
 
+def test_density_model_converges_without_wobble():
+    """ShardedCollider(balance=True) keeps a histogram of the cost over the sorted positions: cuts at
+    different places add up, so the split settles instead of overshooting back and forth."""
+    from collision_b200.sharded import DensityModel, shard_range
+    n = 1 << 20
+    rng = np.random.RandomState(1)
+    rows = np.ones(n, np.int64)                   # 64 clusters of different density in the first 55 %, sparse after
+    span = n * 55 // 100 // 64
+    for k in range(64):
+        rows[k * span:(k + 1) * span] = rng.randint(5, 80)
+    csum = np.concatenate([[0], np.cumsum(rows)])
+    for world in (2, 4, 8):
+        model = DensityModel(n)
+        cut = [shard_range(n, world, r)[0] for r in range(world)] + [n]
+        assert model.cut(world) == cut            # nothing seen yet: the equal-queries split
+        spread = []
+        for frame in range(8):
+            cost = [int(csum[e] - csum[b]) + (e - b) for b, e in zip(cut, cut[1:])]
+            spread.append(max(cost) * world / sum(cost))
+            model.update(cut, cost)
+            cut = model.cut(world)
+            assert cut[0] == 0 and cut[-1] == n and all(a <= b for a, b in zip(cut, cut[1:]))
+        assert spread[0] > 1.7 and spread[1] < 1.2 and max(spread[4:]) < 1.04, (world, spread)
+    # degenerate inputs: empty ranges, zero cost everywhere, one position, more ranks than positions
+    model = DensityModel(10)
+    model.update([0, 0, 10, 10], [0, 50, 0])
+    assert model.cut(2) == [0, 5, 10]
+    model.update([0, 5, 10], [0, 0])
+    assert model.cut(2) == [0, 5, 10]             # no cost seen: equal queries
+    assert DensityModel(1).cut(4) in ([0, 0, 0, 0, 1], [0, 1, 1, 1, 1])
+    with pytest.raises(ValueError):
+        DensityModel(10).update([0, 6, 5, 10], [1, 1, 1])
+    with pytest.raises(ValueError):
+        DensityModel(10).update([0, 5, 9], [1, 1])
+
+
+def test_sharded_collider_recut_bookkeeping():
+    """The host-side step ShardedCollider(balance=True) takes after the totals are gathered (no GPU needed:
+    the object is assembled by hand around the bookkeeping fields)."""
+    from collision_b200.sharded import DensityModel, ShardedCollider, shard_range
+    n, world = 1000, 4
+    ranks = []
+    for rank in range(world):
+        sc = ShardedCollider.__new__(ShardedCollider)
+        sc.size, sc.world, sc.rank, sc.query_weight = n, world, rank, 1
+        sc.edges = [shard_range(n, world, r)[0] for r in range(world)] + [n]
+        sc._density = DensityModel(n)
+        ranks.append(sc)
+    for totals in ([9000, 500, 250, 250], [3000, 3000, 2000, 2000]):
+        for sc in ranks:
+            sc._recut(totals)
+        assert all(sc.edges == ranks[0].edges for sc in ranks)
+        assert all((sc.q_begin, sc.q_end) == (sc.edges[sc.rank], sc.edges[sc.rank + 1]) for sc in ranks)
+        assert ranks[0].edges[0] == 0 and ranks[0].edges[-1] == n
+    assert ranks[0].edges[1] < 250           # the dense first range was cut well below the equal split
+
+
 def _balance_worker(rank, world, port, n, tmpdir):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     dist.init_process_group("gloo", rank=rank, world_size=world)
     try:
         import oracle
-        from collision_b200.sharded import exchange_totals, rebalance_edges, shard_range
+        from collision_b200.sharded import DensityModel, exchange_totals, shard_range
         c, r = _skewed_scene(n)
+        model = DensityModel(n)
         res = oracle.collide(c, r)      # every rank builds the identical tree ("replicate_build")
         edges = [shard_range(n, world, k)[0] for k in range(world)] + [n]
         log = []
@@ -184,7 +242,8 @@ def _balance_worker(rank, world, port, n, tmpdir):
             totals = exchange_totals(torch.tensor([total], dtype=torch.int64)).tolist()
             np.save(os.path.join(tmpdir, "pairs{}_{}.npy".format(frame, rank)), pairs)
             log.append(list(edges) + totals)
-            edges = rebalance_edges(edges, totals, 1)
+            model.update(edges, [t + (e - b) for t, b, e in zip(totals, edges, edges[1:])])
+            edges = model.cut(world)
         np.save(os.path.join(tmpdir, "log{}.npy".format(rank)), np.array(log))
     finally:
         dist.destroy_process_group()
