@@ -98,3 +98,31 @@ def canon(pairs):
 def lexsorted(pairs):
     p = np.asarray(pairs).reshape(-1, 2)
     return p[np.lexsort((p[:, 1], p[:, 0]))]
+
+
+AWKWARD_SHAPES = ("uniform", "clusters", "duplicates", "diagonal", "lattice", "plane")
+
+
+def awkward_scene(shape, seed, dtype='float32'):
+    """Randomised small scenes of the kinds that break LBVH builders: runs of identical Morton codes
+    (duplicates, lattices), collinear and coplanar centres, radii from zero to scene-sized.  Every axis
+    keeps a non-zero extent (two corner spheres): a zero extent is 0/0 in the reference (undefined)."""
+    rs = np.random.RandomState(1000 * AWKWARD_SHAPES.index(shape) + seed)
+    n = int(rs.randint(2, 260))
+    xyz = rs.random_sample((n, 3))
+    if shape == "clusters":
+        xyz = rs.random_sample((4, 3))[rs.randint(0, 4, n)] + rs.normal(0, 0.005, (n, 3))
+    elif shape == "duplicates":
+        xyz = xyz[rs.randint(0, max(n // 8, 1), n)]
+    elif shape == "diagonal":
+        xyz = np.repeat(rs.random_sample((n, 1)), 3, axis=1)
+    elif shape == "lattice":
+        xyz = rs.randint(0, 4, (n, 3)) / 3.0
+    elif shape == "plane":
+        xyz[:, 2] = 0.5
+    c = np.zeros((n, 4), dtype)
+    c[:, :3] = xyz
+    c[0, :3], c[n - 1, :3] = 0.0, 1.0
+    scale = (0.0, 0.01, 1 / np.sqrt(n), 0.6)[seed % 4]
+    r = (rs.random_sample(n) * scale).astype(dtype)
+    return c, r

@@ -232,6 +232,31 @@ def test_count_only_and_overflow(cuda_env, oracle, ordered, layout):
         assert G.canon(got[:cap]) <= G.canon(want['pairs'])
 
 
+@pytest.mark.parametrize("shape", G.AWKWARD_SHAPES)
+def test_awkward_scenes(cuda_env, oracle, shape):
+    """Duplicate Morton codes (repeated points, lattices), collinear and coplanar centres, radii from zero
+    to scene-sized -- the scenes on which the oracle is pinned to the reference's own kernel text
+    (tests/test_oracle_vs_ref.py): every stage and the ordered rows bit for bit."""
+    from collision_b200.collision import Collider
+    dev, cq = cuda_env
+    dt = np.dtype('float32')
+    for seed in range(4):
+        c, r = G.awkward_scene(shape, seed, dt)
+        n = len(c)
+        want = oracle.collide(c, r)
+        collider = Collider(dev, n, 4, 16, dt)
+        total, pairs = run_collider(cuda_env, collider, c, r, want['total'] + 3, dt)
+        np.testing.assert_equal(to_host(collider._codes_bufs[1], 'uint32', (n,)), want['sorted_codes'])
+        np.testing.assert_equal(to_host(collider._ids_bufs[1], 'uint32', (n,)), want['sorted_ids'])
+        nodes = to_host(collider._nodes_buf, Node, (2 * n - 1,))
+        np.testing.assert_equal(nodes[1:]['parent'], want['nodes'][1:]['parent'])
+        np.testing.assert_equal(nodes['data'][:n - 1], want['nodes']['data'][:n - 1])
+        b = to_host(collider._bounds_buf, dt, (2 * n - 1, 2, 4))
+        np.testing.assert_equal(b[:, :, :3], want['bounds'][:, :, :3])
+        assert total == want['total']
+        np.testing.assert_equal(pairs, want['pairs'])
+
+
 def test_program_mismatch(cuda_env):
     # tests/test_collision_py.py:329-336 style: shared programs must match
     from collision_b200.collision import Collider, CollisionProgram

@@ -56,6 +56,10 @@ def test_oracle_equals_reference_kernels(oracle, ref_env, n, clustered):
     else:
         c[:, :3] = rs.random_sample((n, 3))
     r = rs.uniform(0, 1 / np.sqrt(n), n).astype(dt)
+    compare_with_reference_kernels(oracle, lib, dt, c, r)
+
+
+def compare_with_reference_kernels(oracle, lib, dt, c, r):
     rng = oracle.bounds(c)
     want = oracle.collide(c, r)
     codes, order, nodes, b, total, pairs = ref_pipeline(lib, dt, c, r, rng, want['total'] + 5)
@@ -66,6 +70,15 @@ def test_oracle_equals_reference_kernels(oracle, ref_env, n, clustered):
     np.testing.assert_equal(want['bounds'][:, :, :3], b[:, :, :3])
     assert want['total'] == total
     np.testing.assert_equal(want['pairs'], pairs)        # same ORDER too (sequential work-items)
+
+
+@pytest.mark.parametrize("shape", G.AWKWARD_SHAPES)
+def test_oracle_equals_reference_kernels_on_awkward_scenes(oracle, ref_env, shape):
+    """golden_data.awkward_scene: duplicate codes, collinear / coplanar centres, radii from zero to scene-sized."""
+    lib, dt = ref_env
+    for seed in range(6):
+        c, r = G.awkward_scene(shape, seed, dt)
+        compare_with_reference_kernels(oracle, lib, dt, c, r)
 
 
 def test_capacity_clamp(oracle, ref_env):
