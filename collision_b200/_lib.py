@@ -10,7 +10,9 @@ import numpy as np
 import torch
 
 _HERE = Path(__file__).resolve().parent
-_LIB_PATH = _HERE / "libcollision_b200.so"
+import os as _os
+# COL_B200_DEBUG=1: the -DCOL_DEBUG build (python -m collision_b200.build --debug)
+_LIB_PATH = _HERE / ("libcollision_b200_debug.so" if _os.environ.get("COL_B200_DEBUG") == "1" else "libcollision_b200.so")
 _lib = None
 
 COL_F32, COL_F64 = 0, 1
@@ -44,10 +46,18 @@ SIGNATURES = {
     "col_traverse_scratch_bytes": (_sz, [_u32, _u64]),
     "col_traverse_wide_count": (_int, [_vp, _vp, _vp, _vp, _vp, _int, _u32, _u32, _u32, _vp]),
     "col_traverse_wide_pairs": (_int, [_vp, _u64, _u64, _vp, _vp, _vp, _vp, _vp, _int, _u32, _u32, _u32, _vp, _vp]),
+    "col_traverse_wide_pairs_marked": (_int, [_vp, _u64, _u64, _vp, _vp, _vp, _vp, _vp, _int, _u32, _u32, _u32, _vp, _vp, _vp]),
     "col_traverse_wide_write": (_int, [_vp, _u64, _vp, _u64, _vp, _vp, _vp, _vp, _int, _u32, _u32, _u32, _vp]),
     "col_find_offsets": (_int, [_vp, _u64, _u32, _vp, _u64, _u32, _vp]),
     "col_gather": (_int, [_vp, _vp, _vp, _u64, _u32, _u32, _vp]),
     "col_scatter": (_int, [_vp, _vp, _vp, _u64, _u32, _u32, _vp]),
+    "col_compat_local_scan": (_int, [_vp, _vp, _u64, _u32, _vp]),
+    "col_compat_block_scan": (_int, [_vp, _vp, _u64, _u32, _vp]),
+    "col_compat_block_sort": (_int, [_vp, _vp, _vp, _u64, _u32, _u32, _u32, _u32, _u32, _vp]),
+    "col_compat_scatter": (_int, [_vp, _vp, _vp, _vp, _vp, _vp, _u64, _u32, _u32, _u32, _u32, _u32, _vp]),
+    "col_compat_find_offsets": (_int, [_vp, _u64, _u32, _vp, _u32, _vp]),
+    "col_compat_reduce1": (_int, [_vp, _u64, _int, _u32, _vp, _vp, _u32, _vp, _u32, _u32, _vp]),
+    "col_compat_reduce2": (_int, [_vp, _vp, _int, _u32, _vp, _u32, _u32, _vp]),
     "col_fill_u32": (_int, [_vp, _u32, _u64, _vp]),
     "col_range": (_int, [_vp, _u64, _vp]),
     "col_copy": (_int, [_vp, _vp, _u64, _vp]),
@@ -128,6 +138,22 @@ def done(cq):
     return ev
 
 
+def kernel_launcher(fn):
+    """A `program.kernels[name]` entry with PyOpenCL's call convention
+    kernel(cq, global_size, local_size, *args, g_times_l=False, wait_for=None) -> event.
+    `fn(cq, n_threads, local_size_or_None, *args)` enqueues the work; cl.LocalMemory
+    arguments of the reference's kernels are accepted as any placeholder and ignored."""
+    def launch(cq, global_size, local_size, *args, g_times_l=False, wait_for=None, global_offset=None):
+        gs = int(global_size[0]) if not isinstance(global_size, int) else global_size
+        ls = None if local_size is None else (int(local_size[0]) if not isinstance(local_size, int) else local_size)
+        if g_times_l and ls:
+            gs *= ls
+        begin(cq, wait_for)
+        fn(cq, gs, ls, *args)
+        return done(cq)
+    return launch
+
+
 def device_of(ctx):
     dev = torch.device(ctx)
     if dev.type != "cuda":
@@ -140,6 +166,15 @@ def device_of(ctx):
 def alloc_bytes(ctx, nbytes):
     """Private scratch (the reference's HOST_NO_ACCESS cl.Buffer)."""
     return torch.empty(max(int(nbytes), 1), dtype=torch.uint8, device=ctx)
+
+
+def alloc_on(cq, ctx, nbytes):
+    """Scratch used only by work on stream `cq`: allocated with `cq` current, so the caching
+    allocator hands a dropped block out again in cq's order (None: the current stream)."""
+    if cq is None:
+        return alloc_bytes(ctx, nbytes)
+    with torch.cuda.stream(cq):
+        return alloc_bytes(ctx, nbytes)
 
 
 def float_code(dt):

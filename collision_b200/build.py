@@ -44,12 +44,19 @@ def _stale(target, deps):
     return any(d.stat().st_mtime > t for d in deps)
 
 
-def build(force=False, verbose=False):
-    """Compile every .cu (in parallel) and link the shared library.  Returns its path."""
+def build(force=False, verbose=False, debug=False):
+    """Compile every .cu (in parallel) and link the shared library.  Returns its path.
+    debug=True builds libcollision_b200_debug.so (-DCOL_DEBUG: traversal-stack depth traps;
+    loaded instead of the release library when COL_B200_DEBUG=1 is set)."""
+    global OBJ, LIB
+    if debug:
+        OBJ, LIB = HERE / "build_debug", HERE / "libcollision_b200_debug.so"
     headers = list(CSRC.glob("*.cuh")) + [HERE.parent / "include" / "collision_b200.h", Path(__file__)]
     OBJ.mkdir(exist_ok=True)
     nvcc = _nvcc()
     extra = os.environ.get("COL_NVCC_EXTRA", "").split()   # tuning aid (e.g. -DCOL_SORT_THREADS=256)
+    if debug:
+        extra.append("-DCOL_DEBUG")
     jobs = []
     for src in sources():
         obj = OBJ / (src.stem + ".o")
@@ -73,4 +80,4 @@ def build(force=False, verbose=False):
 
 
 if __name__ == "__main__":
-    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))
+    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv, debug="--debug" in sys.argv))

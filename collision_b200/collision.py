@@ -18,6 +18,8 @@ Traversal commits pairs either in the deterministic order of the reference's
 work-items run sequentially (count -> scan -> write; the default) or through one
 atomic counter in arbitrary order exactly like upstream (`ordered=False`).
 """
+import contextlib
+
 import torch
 from numpy import dtype, iinfo
 
@@ -53,44 +55,36 @@ class CollisionProgram(Program):
         L = _lib.lib()
         code = self._code
 
-        def kernel(fn):
-            def launch(cq, global_size, local_size, *args, wait_for=None):
-                _lib.begin(cq, wait_for)
-                fn(cq, *args)
-                return _lib.done(cq)
-            return launch
+        def _range(cq, gs, ls, idxs):
+            _lib.check(L.col_range(_lib.ptr(idxs), gs, _lib.stream_ptr(cq)), "col_range")
 
-        def _range(cq, global_size, local_size, idxs, wait_for=None):
-            _lib.begin(cq, wait_for)
-            _lib.check(L.col_range(_lib.ptr(idxs), int(global_size[0]), _lib.stream_ptr(cq)), "col_range")
-            return _lib.done(cq)
-
-        def calc_codes(cq, codes, coords, rng, n):
+        def calc_codes(cq, gs, ls, codes, coords, rng, n):
             _lib.check(L.col_morton(_lib.ptr(codes), None, _lib.ptr(coords), _lib.ptr(rng), code, n, n,
                                     _lib.stream_ptr(cq)), "col_morton")
 
-        def fill_internal(cq, nodes, ids, n):
+        def fill_internal(cq, gs, ls, nodes, ids, n):
             _lib.check(L.col_fill_leaves(_lib.ptr(nodes), _lib.ptr(ids), n, _lib.stream_ptr(cq)), "col_fill_leaves")
 
-        def generate_bvh(cq, codes, nodes, n):
+        def generate_bvh(cq, gs, ls, codes, nodes, n):
             _lib.check(L.col_build_tree(_lib.ptr(codes), None, _lib.ptr(nodes), n, _lib.stream_ptr(cq)),
                        "col_build_tree")
 
-        def leaf_bounds(cq, bounds, coords, radii, nodes, n):
+        def leaf_bounds(cq, gs, ls, bounds, coords, radii, nodes, n):
             _lib.check(L.col_leaf_bounds(_lib.ptr(bounds), _lib.ptr(coords), _lib.ptr(radii), _lib.ptr(nodes),
                                          code, n, _lib.stream_ptr(cq)), "col_leaf_bounds")
 
-        def internal_bounds(cq, bounds, flags, nodes, n):
+        def internal_bounds(cq, gs, ls, bounds, flags, nodes, n):
             _lib.check(L.col_refit(_lib.ptr(bounds), _lib.ptr(flags), _lib.ptr(nodes), None, None, code, n,
                                    _lib.stream_ptr(cq)), "col_refit")
 
-        def traverse(cq, collisions, nxt, n_collisions, nodes, bounds, n):
+        def traverse(cq, gs, ls, collisions, nxt, n_collisions, nodes, bounds, n):
             _lib.check(L.col_traverse_atomic(_lib.ptr(collisions), _lib.ptr(nxt), n_collisions, _lib.ptr(nodes),
                                              _lib.ptr(bounds), code, n, 0, n, _lib.stream_ptr(cq)),
                        "col_traverse_atomic")
 
+        kernel = _lib.kernel_launcher
         self.kernels = {
-            'range': _range,
+            'range': kernel(_range),
             'calculateCodes': kernel(calc_codes),
             'fillInternal': kernel(fill_internal),
             'generateBVH': kernel(generate_bvh),
@@ -105,6 +99,7 @@ class Collider:
     flag_dtype = dtype('uint32')
     counter_dtype = dtype('uint32')
     id_dtype = dtype('uint32')
+    MAX_GRAPHS = 8      # captured launch sequences kept per Collider (keyed on the buffers of a call)
 
     def __init__(self, ctx, size, ngroups, group_size, coord_dtype=dtype('float32'),
                  program=None, sorter_programs=(None, None), reducer_program=None, ordered=True,
@@ -149,12 +144,22 @@ class Collider:
         self.graph = bool(graph)
         self._graphs = {}
         self._graph_candidate = None
+        # measurement aid: a ctypes array of three cudaEvent_t handles recorded inside the
+        # traversal call (after the walk, the confirmation, the scan); see bench.py
+        self._trv_marks = None
 
     # -- scratch ----------------------------------------------------------
-    def _ensure_scratch(self):
+    def _ensure_scratch(self, cq=None):
         key = (self.size, self.padded_size)
         if self._bufs_for == key:
             return
+        # the scratch is only ever used by work enqueued on `cq`: allocate it with `cq` current so
+        # that the caching allocator re-uses a dropped block in cq's order (a block allocated on
+        # another stream could be handed out again while kernels on cq still read it)
+        with torch.cuda.stream(cq) if cq is not None else contextlib.nullcontext():
+            self._allocate(key)
+
+    def _allocate(self, key):
         ctx = self.program.context
         L = _lib.lib()
         self._graphs.clear()          # captured graphs point into the scratch being replaced
@@ -200,9 +205,9 @@ class Collider:
                        n_collisions, wait_for=None):
         if collisions_buf is None and n_collisions > 0:
             raise ValueError("Invalid collisions_buf for n_collisions > 0")
-        self._ensure_scratch()
+        self._ensure_scratch(cq)
         _lib.begin(cq, wait_for)
-        if self.graph and self.stage_events is None:
+        if self.graph and self.stage_events is None and self._trv_marks is None:
             key = (cq.cuda_stream, self.size, n_collisions, _lib.ptr(coords_buf), _lib.ptr(radii_buf),
                    _lib.ptr(n_collisions_buf), _lib.ptr(collisions_buf))
             entry = self._graphs.get(key)
@@ -214,6 +219,8 @@ class Collider:
                     self._enqueue(cq, coords_buf, radii_buf, n_collisions_buf, collisions_buf, n_collisions)
                 entry = self._graphs[key] = (g, self.kernel_launches - before)
                 self.kernel_launches = before
+                while len(self._graphs) > self.MAX_GRAPHS:     # a caller cycling through many buffers:
+                    self._graphs.pop(next(iter(self._graphs)))  # forget the oldest capture
                 # (buffers named in the key are referenced by the graph: the caller keeps them alive,
                 #  as it must for any enqueued work)
             if entry is not None:
@@ -247,7 +254,7 @@ class Collider:
         # upstream keeps the scene bounds in slot 0 of the Bound array (dual use, collision.py:74-78);
         # the fast path needs them beyond the refit (grid of the traversal records), so they get a buffer
         scene = self._scene_buf if self.fast else self._bounds_buf
-        _lib.check(L.col_bounds(P(coords_buf), n, code, 4, P(scene), P(self.reducer._ensure_scratch()), S),
+        _lib.check(L.col_bounds(P(coords_buf), n, code, 4, P(scene), P(self.reducer._ensure_scratch(cq)), S),
                    "col_bounds")
         mark(cq, "bounds", 1)
         _lib.check(L.col_morton(P(self._codes_bufs[0]), P(self._ids_bufs[0]), P(coords_buf), P(scene),
@@ -255,7 +262,7 @@ class Collider:
         mark(cq, "morton", 1)
         # padding keys are not needed by this sort: only the n real keys move
         _lib.check(L.col_sort_pairs(P(self._codes_bufs[0]), P(self._codes_bufs[1]), P(self._ids_bufs[0]),
-                                    P(self._ids_bufs[1]), n, 4, 4, MORTON_BITS, P(self.sorter._ensure_scratch()), S),
+                                    P(self._ids_bufs[1]), n, 4, 4, MORTON_BITS, P(self.sorter._ensure_scratch(cq=cq)), S),
                    "col_sort_pairs")
         mark(cq, "sort", 2 + (MORTON_BITS + 7) // 8)   # histogram + digit bases + one launch per digit
 
@@ -284,14 +291,18 @@ class Collider:
         L, P, S = _lib.lib(), _lib.ptr, _lib.stream_ptr(cq)
         need = L.col_traverse_scratch_bytes(q_end - q_begin, n_collisions)
         if need > self._trv_scratch_bytes:   # (grows with the rows per query: deeper per-query stash)
-            self._trv_scratch = _lib.alloc_bytes(self.program.context, need)
+            with torch.cuda.stream(cq):      # allocated in cq's order, like the rest of the scratch
+                self._trv_scratch = _lib.alloc_bytes(self.program.context, need)
             self._trv_scratch_bytes = need
             self._graphs.clear()
             self._graph_candidate = None
-        _lib.check(L.col_traverse_wide_pairs(P(collisions_buf), n_collisions, base, P(self._total_buf),
-                                             P(self._wide_buf), P(self._bounds_buf), P(self._scene_buf),
-                                             P(self._ids_bufs[1]), self.program._code, self.size, q_begin, q_end,
-                                             P(self._trv_scratch), S), "col_traverse_wide_pairs")
+        args = (P(collisions_buf), n_collisions, base, P(self._total_buf), P(self._wide_buf), P(self._bounds_buf),
+                P(self._scene_buf), P(self._ids_bufs[1]), self.program._code, self.size, q_begin, q_end,
+                P(self._trv_scratch), S)
+        if self._trv_marks is not None and n_collisions:
+            _lib.check(L.col_traverse_wide_pairs_marked(*args, self._trv_marks), "col_traverse_wide_pairs_marked")
+        else:
+            _lib.check(L.col_traverse_wide_pairs(*args), "col_traverse_wide_pairs")
         self._mark(cq, "traverse_pairs" if n_collisions else "traverse_count", 4 if n_collisions else 1)
 
     def _traverse_fast(self, cq, coords_buf, radii_buf, n_collisions_buf, collisions_buf, n_collisions):

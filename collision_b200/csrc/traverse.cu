@@ -99,7 +99,12 @@ traverse_kernel(uint32_t* __restrict__ pairs, uint32_t* __restrict__ counts_or_c
             idx = stack[--sp];
         } else {
             idx = ta ? ca : cb;
-            if (ta && tb) stack[sp++] = cb;
+            if (ta && tb) {
+#ifdef COL_DEBUG   // (collision.cl:186: the reference's stack is unguarded too)
+                if (sp >= 64) __trap();
+#endif
+                stack[sp++] = cb;
+            }
         }
     } while (idx != 0xFFFFFFFFu);
 

@@ -121,7 +121,12 @@ __device__ __forceinline__ uint32_t visit(const unsigned char* __restrict__ wide
     }
     const bool ta = oa && !la, tb = ob && !lb;
     if (!ta && !tb) return stack[--sp];
-    if (ta && tb) stack[sp++] = cb;
+    if (ta && tb) {
+#ifdef COL_DEBUG   // collision.cl:186 has the same unguarded 64-entry stack; a debug build traps instead of overrunning
+        if (sp >= 64) __trap();
+#endif
+        stack[sp++] = cb;
+    }
     return ta ? ca : cb;
 }
 
@@ -411,8 +416,11 @@ COL_API int col_traverse_wide_count(uint64_t* total, uint32_t* counts, const voi
 template <typename T>
 static int pairs_impl(uint32_t* pairs, uint64_t capacity, uint64_t base, unsigned long long* total,
                       const unsigned char* w, const T* bounds, const T* scene, const uint32_t* ids, uint32_t n,
-                      uint32_t q_begin, uint32_t q_end, char* sc, void* stream) {
+                      uint32_t q_begin, uint32_t q_end, char* sc, void* stream, void* const* marks) {
     cudaStream_t s = col_stream(stream);
+    auto mark = [&](int k) -> int {   // optional stage marks (cudaEvent_t handles) for the bench's compaction figure
+        return (marks && marks[k]) ? (int)cudaEventRecord((cudaEvent_t)marks[k], s) : 0;
+    };
     const uint32_t nq = q_end - q_begin;
     const uint32_t depth = stash_depth(nq, capacity);
     const PairsLayout L = pairs_layout(nq, depth);
@@ -422,19 +430,22 @@ static int pairs_impl(uint32_t* pairs, uint64_t capacity, uint64_t base, unsigne
     const uint32_t pf = 64;   // 128-byte lines of the block's own record window prefetched to L1 (0..256: +4 % at 64)
     candidates_kernel<T><<<blocks, TRV_THREADS, 0, s>>>(counts, stash, w, bounds, scene, n, q_begin, q_end, pf, depth);
     COL_CHECK_LAUNCH();
+    COL_CUDA((cudaError_t)mark(0));
     confirm_kernel<T><<<blocks, TRV_THREADS, 0, s>>>(total, counts, stash, w, bounds, scene, n, q_begin, q_end, depth);
     COL_CHECK_LAUNCH();
+    COL_CUDA((cudaError_t)mark(1));
     const int rc = col_exclusive_scan_u32(counts, nq, nullptr, sc + L.scan, stream);
     if (rc) return rc;
+    COL_CUDA((cudaError_t)mark(2));
     emit_kernel<T><<<blocks, TRV_THREADS, 0, s>>>(pairs, capacity, base, counts, total, stash, w, bounds, scene, ids, n, q_begin, q_end, depth);
     COL_CHECK_LAUNCH();
     return 0;
 }
 
-COL_API int col_traverse_wide_pairs(uint32_t* pairs, uint64_t capacity, uint64_t base, uint64_t* total_out,
-                                    const void* wide, const void* bounds, const void* scene2x4,
-                                    const uint32_t* ids_sorted, int dtype, uint32_t n, uint32_t q_begin,
-                                    uint32_t q_end, void* scratch, void* stream) {
+static int wide_pairs(uint32_t* pairs, uint64_t capacity, uint64_t base, uint64_t* total_out,
+                      const void* wide, const void* bounds, const void* scene2x4,
+                      const uint32_t* ids_sorted, int dtype, uint32_t n, uint32_t q_begin,
+                      uint32_t q_end, void* scratch, void* stream, void* const* marks) {
     if (!wide || !bounds || !scene2x4 || !ids_sorted || !scratch || !total_out || bad_range(n, q_begin, q_end) ||
         (!pairs && capacity))
         return COL_ERR_BAD_ARG;
@@ -447,8 +458,24 @@ COL_API int col_traverse_wide_pairs(uint32_t* pairs, uint64_t capacity, uint64_t
     const unsigned char* w = (const unsigned char*)wide;
     char* sc = reinterpret_cast<char*>(scratch);
     if (dtype == COL_F32)
-        return pairs_impl<float>(pairs, capacity, base, total, w, (const float*)bounds, (const float*)scene2x4, ids_sorted, n, q_begin, q_end, sc, stream);
-    return pairs_impl<double>(pairs, capacity, base, total, w, (const double*)bounds, (const double*)scene2x4, ids_sorted, n, q_begin, q_end, sc, stream);
+        return pairs_impl<float>(pairs, capacity, base, total, w, (const float*)bounds, (const float*)scene2x4, ids_sorted, n, q_begin, q_end, sc, stream, marks);
+    return pairs_impl<double>(pairs, capacity, base, total, w, (const double*)bounds, (const double*)scene2x4, ids_sorted, n, q_begin, q_end, sc, stream, marks);
+}
+
+COL_API int col_traverse_wide_pairs(uint32_t* pairs, uint64_t capacity, uint64_t base, uint64_t* total_out,
+                                    const void* wide, const void* bounds, const void* scene2x4,
+                                    const uint32_t* ids_sorted, int dtype, uint32_t n, uint32_t q_begin,
+                                    uint32_t q_end, void* scratch, void* stream) {
+    return wide_pairs(pairs, capacity, base, total_out, wide, bounds, scene2x4, ids_sorted, dtype, n, q_begin, q_end,
+                      scratch, stream, nullptr);
+}
+
+COL_API int col_traverse_wide_pairs_marked(uint32_t* pairs, uint64_t capacity, uint64_t base, uint64_t* total_out,
+                                           const void* wide, const void* bounds, const void* scene2x4,
+                                           const uint32_t* ids_sorted, int dtype, uint32_t n, uint32_t q_begin,
+                                           uint32_t q_end, void* scratch, void* stream, void* const* h_marks3) {
+    return wide_pairs(pairs, capacity, base, total_out, wide, bounds, scene2x4, ids_sorted, dtype, n, q_begin, q_end,
+                      scratch, stream, h_marks3);
 }
 
 COL_API int col_traverse_wide_write(uint32_t* pairs, uint64_t capacity, const uint32_t* offsets, uint64_t base,

@@ -17,6 +17,17 @@ class IndexProgram(Program):
         if self.index_dtype.itemsize not in (4, 8):
             raise ValueError("Unsupported index dtype: {} (uint32 / uint64)".format(self.index_dtype))
         super().__init__(ctx)
+        L, P = _lib.lib(), _lib.ptr
+        vb, ib = dtype_sizeof(self.value_dtype), self.index_dtype.itemsize
+
+        # kernel-level contracts of collision/index.cl:1-13: one work-item per element
+        def gather(cq, gs, ls, in_values, indices, out_values):
+            _lib.check(L.col_gather(P(in_values), P(indices), P(out_values), gs, vb, ib, _lib.stream_ptr(cq)), "col_gather")
+
+        def scatter(cq, gs, ls, in_values, indices, out_values):
+            _lib.check(L.col_scatter(P(in_values), P(indices), P(out_values), gs, vb, ib, _lib.stream_ptr(cq)), "col_scatter")
+
+        self.kernels = {'gather': _lib.kernel_launcher(gather), 'scatter': _lib.kernel_launcher(scatter)}
 
 
 class Indexer:

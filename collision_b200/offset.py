@@ -20,6 +20,16 @@ class OffsetProgram(Program):
             if dt.itemsize not in (4, 8):
                 raise ValueError("Unsupported dtype: {} (uint32 / uint64)".format(dt))
         super().__init__(ctx)
+        L, P = _lib.lib(), _lib.ptr
+        vb, ob = self.value_dtype.itemsize, self.offset_dtype.itemsize
+
+        # kernel-level contract of collision/offset.cl:3-12 (tests/test_offset.py:12-47 upstream):
+        # n_values - 1 work-items, no fill
+        def find_offsets(cq, gs, ls, values, offsets):
+            _lib.check(L.col_compat_find_offsets(P(values), gs, vb, P(offsets), ob, _lib.stream_ptr(cq)),
+                       "col_compat_find_offsets")
+
+        self.kernels = {'find_offsets': _lib.kernel_launcher(find_offsets)}
 
 
 class OffsetFinder:

@@ -31,6 +31,24 @@ class RadixProgram(Program):
         if self.key_dtype.itemsize not in (4, 8):
             raise ValueError("Unsupported key dtype: {} (uint32 / uint64)".format(self.key_dtype))
         super().__init__(ctx)
+        kb, vb = self.key_dtype.itemsize, dtype_sizeof(self.value_dtype)
+        L, P = _lib.lib(), _lib.ptr
+
+        # the reference's kernel-level contracts (collision/radix.py:11-15; tests/test_radix.py:34-53
+        # upstream launch them directly): local-memory arguments are placeholders here
+        def block_sort(cq, gs, ls, keys, _lk_in, _lk_out, values, _lv_in, _lv_out, histogram, _lh, _count,
+                       radix_bits, radix_pass):
+            _lib.check(L.col_compat_block_sort(P(keys), P(values), P(histogram), gs // ls, 2 * ls, kb, vb,
+                                               int(radix_bits), int(radix_pass), _lib.stream_ptr(cq)),
+                       "col_compat_block_sort")
+
+        def scatter(cq, gs, ls, keys, out_keys, values, out_values, offset, _lo, histogram, _lh,
+                    radix_bits, radix_pass):
+            _lib.check(L.col_compat_scatter(P(keys), P(out_keys), P(values), P(out_values), P(offset), P(histogram),
+                                            gs // ls, 2 * ls, kb, vb, int(radix_bits), int(radix_pass),
+                                            _lib.stream_ptr(cq)), "col_compat_scatter")
+
+        self.kernels = {'block_sort': _lib.kernel_launcher(block_sort), 'scatter': _lib.kernel_launcher(scatter)}
 
 
 class RadixSorter:
@@ -66,10 +84,10 @@ class RadixSorter:
         """Bytes per payload slot; a 3-vector travels in a 4-lane slot (radix.py:122-126)."""
         return dtype_sizeof(self.program.value_dtype)
 
-    def _ensure_scratch(self, size=None):
+    def _ensure_scratch(self, size=None, cq=None):
         need = _lib.lib().col_sort_scratch_bytes(size or self.size, self.program.key_dtype.itemsize, self.value_size)
         if self._scratch is None or self._scratch.numel() < need:
-            self._scratch = _lib.alloc_bytes(self.program.context, need)
+            self._scratch = _lib.alloc_on(cq, self.program.context, need)
         return self._scratch
 
     @staticmethod
@@ -121,7 +139,7 @@ class RadixSorter:
             _lib.ptr(in_values_buf) if have_values else None,
             _lib.ptr(out_values_buf) if have_values else None,
             self.size, self.program.key_dtype.itemsize, self.value_size if have_values else 0,
-            end_bit, _lib.ptr(self._ensure_scratch()), _lib.stream_ptr(cq)), "col_sort_pairs")
+            end_bit, _lib.ptr(self._ensure_scratch(cq=cq)), _lib.stream_ptr(cq)), "col_sort_pairs")
         return _lib.done(cq)
 
     def radix_pass(self, cq, keys_buf, out_keys_buf, in_values_buf, out_values_buf, radix_pass,
@@ -135,5 +153,5 @@ class RadixSorter:
             _lib.ptr(in_values_buf) if have_values else None,
             _lib.ptr(out_values_buf) if have_values else None,
             self.size, self.program.key_dtype.itemsize, self.value_size if have_values else 0,
-            self.radix_bits, radix_pass, _lib.ptr(self._ensure_scratch()), _lib.stream_ptr(cq)), "col_radix_pass")
+            self.radix_bits, radix_pass, _lib.ptr(self._ensure_scratch(cq=cq)), _lib.stream_ptr(cq)), "col_radix_pass")
         return _lib.done(cq)

@@ -21,6 +21,18 @@ class PrefixScanProgram(Program):
 
     def __init__(self, ctx):
         super().__init__(ctx)
+        L, P = _lib.lib(), _lib.ptr
+
+        # kernel-level contracts of collision/scan.cl:5-36 (tests/test_scan.py:8-21 upstream)
+        def local_scan(cq, gs, ls, data, _local, block_sums):
+            _lib.check(L.col_compat_local_scan(P(data), P(block_sums), gs // ls, 2 * ls, _lib.stream_ptr(cq)),
+                       "col_compat_local_scan")
+
+        def block_scan(cq, gs, ls, data, block_sums):
+            _lib.check(L.col_compat_block_scan(P(data), P(block_sums), 2 * gs, 2 * ls, _lib.stream_ptr(cq)),
+                       "col_compat_block_scan")
+
+        self.kernels = {'local_scan': _lib.kernel_launcher(local_scan), 'block_scan': _lib.kernel_launcher(block_scan)}
 
 
 class PrefixScanner:
@@ -37,10 +49,10 @@ class PrefixScanner:
         self.program = program
         self._scratch = None    # device scratch is allocated on first use
 
-    def _ensure_scratch(self):
+    def _ensure_scratch(self, cq=None):
         need = _lib.lib().col_scan_scratch_bytes(self.size)
         if self._scratch is None or self._scratch.numel() < need:
-            self._scratch = _lib.alloc_bytes(self.program.context, need)
+            self._scratch = _lib.alloc_on(cq, self.program.context, need)
         return self._scratch
 
     @staticmethod
@@ -75,6 +87,6 @@ class PrefixScanner:
     def prefix_sum(self, cq, values_buf, wait_for=None):
         _lib.begin(cq, wait_for)
         _lib.check(_lib.lib().col_exclusive_scan_u32(
-            _lib.ptr(values_buf), self.size, None, _lib.ptr(self._ensure_scratch()), _lib.stream_ptr(cq)),
+            _lib.ptr(values_buf), self.size, None, _lib.ptr(self._ensure_scratch(cq)), _lib.stream_ptr(cq)),
             "col_exclusive_scan_u32")
         return _lib.done(cq)

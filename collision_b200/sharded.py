@@ -143,10 +143,16 @@ def broadcast_buffers(buffers, src=0, group=None):
 
 
 def gather_slices(buf, per_item, n, group=None):
-    """In-place all-gather of a scene array: `buf` holds n items of `per_item` elements and rank
-    r has filled items [n*r/k, n*(r+1)/k) (shard_range); afterwards every rank holds all n."""
+    """In-place all-gather of a scene array: `buf` holds n items of `per_item` BYTES each and
+    rank r has filled items [n*r/k, n*(r+1)/k) (shard_range); afterwards every rank holds all n.
+    `buf` may be a typed tensor or raw bytes (like every other entry point): it is viewed as
+    bytes, and must hold exactly n * per_item of them."""
     world, rank = dist.get_world_size(group), dist.get_rank(group)
-    flat = buf.view(-1)
+    if not buf.is_contiguous():
+        raise ValueError("buffer must be contiguous")
+    flat = buf.view(torch.uint8).reshape(-1)
+    if flat.numel() != n * per_item:
+        raise ValueError("buffer holds {} bytes, expected {} items x {} bytes".format(flat.numel(), n, per_item))
     if n % world == 0:
         m = n // world * per_item
         mine = flat[rank * m:(rank + 1) * m]
@@ -174,7 +180,7 @@ class ShardedCollider:
     MODES = ("broadcast_tree", "replicate_build", "gather_inputs")
 
     def __init__(self, ctx, size, ngroups, group_size, coord_dtype=dtype('float32'), group=None, src=0,
-                 mode="broadcast_tree", balance=False, query_weight=1):
+                 mode="broadcast_tree", balance=False, query_weight=1, graph=False):
         """mode "broadcast_tree" (north_star): rank `src` sorts, builds and refits; the
         traversal data (68 B per sphere) is broadcast.
         mode "replicate_build": the INPUT (coords + radii, 20 B per sphere) is broadcast
@@ -184,11 +190,17 @@ class ShardedCollider:
         mode "gather_inputs": as "replicate_build", but the scene arrives sharded -- every rank
         owns the spheres [size*r/k, size*(r+1)/k) -- and is all-gathered in place (the same
         bytes over NVLink, but k host links feed it instead of one).
-        balance=True: after every call (with sync_totals) the query ranges of the next call are
-        re-cut from the all-gathered row totals (cost of a range = rows + query_weight * queries,
-        accumulated in a `DensityModel`), so that a clustered scene called frame after frame
-        converges on equal work per rank; the first call uses the equal-queries split.  The rows
-        and their order are the same for any split."""
+        balance=True: after every call (with sync_totals) that WRITES rows the query ranges of
+        the next call are re-cut from the all-gathered row totals (cost of a range = rows +
+        query_weight * queries, accumulated in a `DensityModel`), so that a clustered scene
+        called frame after frame converges on equal work per rank; the first call uses the
+        equal-queries split.  Count-only calls (the sizing call of the reference's
+        count-then-allocate protocol) never re-cut: the `local_pairs` they report describes the
+        range the next call walks.  Because a re-cut moves rows between ranks from one frame to
+        the next, size `collisions_buf` with headroom (see `suggested_capacity`) and check
+        `overflowed` after a writing call.  The rows and their order are the same for any split.
+        graph=True: calls with sync_totals=False replay the whole step -- kernels AND NCCL
+        collectives -- as one CUDA graph from the second call with the same buffers on."""
         if mode not in self.MODES:
             raise ValueError("mode must be one of {}".format(self.MODES))
         self.mode = mode
@@ -206,7 +218,21 @@ class ShardedCollider:
         self.local_pairs = 0
         self.pair_base = 0
         self.total_pairs = 0
+        self.overflowed = False       # last writing call (with sync_totals): local_pairs > n_collisions
         self._totals = None
+        self.graph = bool(graph)
+        self._graphs = {}
+        self._graph_candidate = None
+        self.graph_replays = 0
+
+    def suggested_capacity(self, headroom=1.5):
+        """Rows to make room for on this rank after a count-only call: with balance=True the
+        next frames move the cuts, so a rank may receive up to its fair share of the whole list
+        plus the drift of the density model -- `headroom` x max(local, total / world)."""
+        fair = -(-self.total_pairs // self.world)
+        if not self.balance:
+            return self.local_pairs
+        return int(headroom * max(self.local_pairs, fair)) + 1
 
     # instrumentation is the inner collider's
     @property
@@ -242,8 +268,47 @@ class ShardedCollider:
         if collisions_buf is None and n_collisions > 0:
             raise ValueError("Invalid collisions_buf for n_collisions > 0")
         c = self.collider
-        c._ensure_scratch()
+        c._ensure_scratch(cq)
         _lib.begin(cq, wait_for)
+        use_graph = self.graph and not sync_totals and c.stage_events is None
+        if use_graph:
+            key = (cq.cuda_stream, self.size, n_collisions, self.q_begin, self.q_end, _lib.ptr(coords_buf),
+                   _lib.ptr(radii_buf), _lib.ptr(n_collisions_buf), _lib.ptr(collisions_buf), c._trv_scratch_bytes)
+            entry = self._graphs.get(key)
+            if entry is None and self._graph_candidate == key:
+                # second call with this signature (scratch allocated, NCCL communicator warm): capture
+                g = torch.cuda.CUDAGraph()
+                before = c.kernel_launches
+                with torch.cuda.graph(g, stream=cq, capture_error_mode="thread_local"):
+                    self._enqueue(cq, coords_buf, radii_buf, n_collisions_buf, collisions_buf, n_collisions)
+                entry = self._graphs[key] = (g, c.kernel_launches - before, self._totals)
+                c.kernel_launches = before
+                while len(self._graphs) > Collider.MAX_GRAPHS:
+                    self._graphs.pop(next(iter(self._graphs)))
+            if entry is not None:
+                with torch.cuda.stream(cq):
+                    entry[0].replay()
+                c.kernel_launches += entry[1]
+                self._totals = entry[2]
+                self.graph_replays += 1
+                return _lib.done(cq)
+            self._graph_candidate = key
+        self._enqueue(cq, coords_buf, radii_buf, n_collisions_buf, collisions_buf, n_collisions)
+        ev = _lib.done(cq)
+        if sync_totals:     # host-visible bookkeeping (one small readback)
+            ev.synchronize()
+            t = self._totals.tolist()
+            self.local_pairs = t[self.rank]
+            self.pair_base = sum(t[:self.rank])
+            self.total_pairs = sum(t)
+            if n_collisions > 0:
+                self.overflowed = self.local_pairs > n_collisions
+                if self.balance:     # (count-only calls never move the cuts: see __init__)
+                    self._recut(t)
+        return ev
+
+    def _enqueue(self, cq, coords_buf, radii_buf, n_collisions_buf, collisions_buf, n_collisions):
+        c = self.collider
         c._mark(cq, "begin", 0)
         with torch.cuda.stream(cq):
             if self.mode == "broadcast_tree":
@@ -254,8 +319,9 @@ class ShardedCollider:
                 c._mark(cq, "broadcast", 0)
             else:
                 if self.mode == "gather_inputs":
-                    gather_slices(coords_buf, 4, self.size, self.group)
-                    gather_slices(radii_buf, 1, self.size, self.group)
+                    isz = c.program.coord_dtype.itemsize
+                    gather_slices(coords_buf, 4 * isz, self.size, self.group)
+                    gather_slices(radii_buf, isz, self.size, self.group)
                 else:
                     broadcast_buffers([coords_buf, radii_buf], self.src, self.group)
                 c._mark(cq, "broadcast", 0)
@@ -266,15 +332,4 @@ class ShardedCollider:
             total = self._totals.sum().reshape(1)
             _lib.check(_lib.lib().col_copy(_lib.ptr(n_collisions_buf), _lib.ptr(total), 4, _lib.stream_ptr(cq)),
                        "col_copy")
-            total.record_stream(cq)
             c._mark(cq, "all_gather", 0)
-        ev = _lib.done(cq)
-        if sync_totals:     # host-visible bookkeeping (one small readback)
-            ev.synchronize()
-            t = self._totals.tolist()
-            self.local_pairs = t[self.rank]
-            self.pair_base = sum(t[:self.rank])
-            self.total_pairs = sum(t)
-            if self.balance:
-                self._recut(t)
-        return ev

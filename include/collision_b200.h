@@ -210,6 +210,14 @@ int col_traverse_wide_pairs(uint32_t* pairs, uint64_t capacity, uint64_t base, u
                             const void* wide, const void* bounds, const void* scene2x4,
                             const uint32_t* ids_sorted, int dtype, uint32_t n, uint32_t q_begin,
                             uint32_t q_end, void* scratch, void* stream);
+/* The same call with optional stage marks: h_marks3 is a HOST array of three cudaEvent_t handles
+ * (any may be NULL) recorded on `stream` after the walk, after the exact confirmation and after
+ * the scan of the row counts -- what follows the third is the emit.  Measurement aid (bench.py's
+ * "compaction" figure: scan + emit); it launches exactly the kernels of col_traverse_wide_pairs. */
+int col_traverse_wide_pairs_marked(uint32_t* pairs, uint64_t capacity, uint64_t base, uint64_t* total_out,
+                                   const void* wide, const void* bounds, const void* scene2x4,
+                                   const uint32_t* ids_sorted, int dtype, uint32_t n, uint32_t q_begin,
+                                   uint32_t q_end, void* scratch, void* stream, void* const* h_marks3);
 int col_traverse_wide_write(uint32_t* pairs, uint64_t capacity, const uint32_t* offsets, uint64_t base,
                             const void* wide, const void* bounds, const void* scene2x4,
                             const uint32_t* ids_sorted, int dtype, uint32_t n, uint32_t q_begin,
@@ -231,6 +239,49 @@ int col_gather(const void* in, const void* idx, void* out, uint64_t n, uint32_t 
                uint32_t index_bytes, void* stream);
 int col_scatter(const void* in, const void* idx, void* out, uint64_t n, uint32_t value_bytes,
                 uint32_t index_bytes, void* stream);
+
+/* ------------------------------------------- kernel-level contracts (compat.cu)
+ * Upstream's tests launch the kernels of the non-collision programs directly, with the
+ * reference's own launch geometry ("the kernel-level argument/layout
+ * contract is public too").  These entry points stand behind `program.kernels[name]` of
+ * RadixProgram, PrefixScanProgram, ReductionProgram and OffsetProgram; the hot path
+ * (col_sort_pairs, col_exclusive_scan_u32, col_bounds, col_find_offsets) never calls them.
+ * One CUDA block per OpenCL work-group; `items_per_group` = 2 * local_size.
+ *
+ * col_compat_local_scan   local_scan   collision/scan.cl:5-30: every group's exclusive scan in
+ *                         place, group totals to block_sums[group] (block_sums may be NULL).
+ * col_compat_block_scan   block_scan   collision/scan.cl:32-36: data[i] += block_sums[group of i].
+ * col_compat_block_sort   block_sort   collision/radix.cl:48-102: every group stable-sorted by
+ *                         the digit in place (values, when given, move with their keys; value_bytes
+ *                         a multiple of 4); histogram[digit * n_groups + group] = the group's counts.
+ * col_compat_scatter      scatter      collision/radix.cl:104-139: block-sorted groups to
+ *                         out[offset[d * n_groups + g] + i - first slot of digit d in the group].
+ * col_compat_find_offsets find_offsets collision/offset.cl:3-12, literally (thread g: offsets[i] = g + 1
+ *                         for i in (values[g], values[g + 1]]; offsets[g] = 0 for g <= values[0]); the
+ *                         fill is the host's (collision/offset.py:43-46).
+ * col_compat_reduce1/2    bounds1 / bounds2  collision/reduce.cl:5-58 for ANY accumulator list
+ *                         (collision/reduce.py:9-22): h_ops[a] in {0: min, 1: max, 2: ADD}, h_inits[a] the
+ *                         initialiser (HOST arrays, n_acc <= 8); reduce1 = ngroups x group_size
+ *                         threads, grid-stride, group_accs[group][acc][lane]; reduce2 = one group of
+ *                         `ngroups` threads folding the partials IN PLACE with upstream's halving loop
+ *                         -- a non-power-of-two ngroups drops the tail partials exactly as upstream
+ *                         (reduce.cl:42-52).  dtype: COL_F32 ... COL_I64; lanes <= 16. */
+int col_compat_local_scan(uint32_t* data, uint32_t* block_sums, uint64_t n_groups, uint32_t items_per_group,
+                          void* stream);
+int col_compat_block_scan(uint32_t* data, const uint32_t* block_sums, uint64_t n_items, uint32_t items_per_group,
+                          void* stream);
+int col_compat_block_sort(void* keys, void* values, uint32_t* histogram, uint64_t n_groups, uint32_t items_per_group,
+                          uint32_t key_bytes, uint32_t value_bytes, uint32_t radix_bits, uint32_t pass, void* stream);
+int col_compat_scatter(const void* keys, void* out_keys, const void* values, void* out_values, const uint32_t* offset,
+                       const uint32_t* histogram, uint64_t n_groups, uint32_t items_per_group, uint32_t key_bytes,
+                       uint32_t value_bytes, uint32_t radix_bits, uint32_t pass, void* stream);
+int col_compat_find_offsets(const void* values, uint64_t n_threads, uint32_t value_bytes, void* offsets,
+                            uint32_t offset_bytes, void* stream);
+int col_compat_reduce1(const void* values, uint64_t n, int dtype, uint32_t lanes, const int* h_ops,
+                       const double* h_inits, uint32_t n_acc, void* group_accs, uint32_t ngroups, uint32_t group_size,
+                       void* stream);
+int col_compat_reduce2(void* group_accs, void* output, int dtype, uint32_t lanes, const int* h_ops, uint32_t n_acc,
+                       uint32_t ngroups, void* stream);
 
 /* utility: u32 fill (cl.enqueue_fill_buffer sites, e.g. collision/offset.py:43) */
 int col_fill_u32(uint32_t* dst, uint32_t value, uint64_t n, void* stream);

@@ -22,12 +22,34 @@ Node = np.dtype([('parent', 'uint32'), ('right_edge', 'uint32'), ('data', 'uint3
 NO_NODE = 0xFFFFFFFF
 
 
+def _cpu_stamp():
+    """Identifies the host ISA the library was compiled for (-march=native)."""
+    import hashlib
+    flags = ""
+    try:
+        for line in open("/proc/cpuinfo"):
+            if line.startswith(("flags", "Features", "model name")):
+                flags += line
+                if line.startswith(("flags", "Features")):
+                    break
+    except OSError:
+        pass
+    return hashlib.sha1(flags.encode()).hexdigest()[:16]
+
+
 def build(force=False):
-    """Compile liboracle.so (and oracle/_ref when /root/reference exists)."""
+    """Compile liboracle.so (and oracle/_ref when /root/reference exists) with
+    -O3 -march=native; rebuilt when the source is newer or when the host CPU is not the
+    one the library was built on (the built file travels to the GPU box)."""
     so = _HERE / "liboracle.so"
     src = _HERE / "collision_oracle.c"
-    if force or not so.exists() or so.stat().st_mtime < src.stat().st_mtime:
-        subprocess.run(["make", "-C", str(_HERE), "-s", "all"], check=True)
+    stamp = _HERE / "liboracle.stamp"
+    want = _cpu_stamp()
+    have = stamp.read_text().strip() if stamp.exists() else ""
+    stale = not so.exists() or so.stat().st_mtime < max(src.stat().st_mtime, (_HERE / "Makefile").stat().st_mtime)
+    if force or stale or have != want:
+        subprocess.run(["make", "-C", str(_HERE), "-s", "-B", "all"], check=True)
+        stamp.write_text(want + "\n")
     return so
 
 
@@ -44,6 +66,8 @@ def lib():
         _LIB.orc_brute_force_f32.restype = C.c_uint64
         _LIB.orc_brute_force_f64.restype = C.c_uint64
         _LIB.orc_pipeline_f32.restype = C.c_uint64
+        _LIB.orc_pipeline_f32_single.restype = C.c_uint64
+        _LIB.orc_traverse_f32_single.restype = C.c_uint64
     return _LIB
 
 
@@ -62,6 +86,16 @@ def _sfx(dt):
 
 def num_threads():
     return lib().orc_num_threads()
+
+
+def set_num_threads(nt=None):
+    """Use `nt` OpenMP threads (default: every core this process may run on), whatever
+    OMP_NUM_THREADS says -- torchrun exports OMP_NUM_THREADS=1.  Returns the count in use."""
+    import os
+    if nt is None:
+        nt = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    lib().orc_set_num_threads(C.c_int(int(nt)))
+    return num_threads()
 
 
 # ------------------------------------------------------------------ stages
@@ -218,15 +252,25 @@ class Pipeline:
         self.flags = np.zeros(2 * n - 1, np.uint32)
         self.offsets = np.zeros(n, np.uint64)
 
-    def run(self, coords4, radii, capacity=0):
-        """Returns (total, pairs[:min(total, capacity)])."""
+    def run(self, coords4, radii, capacity=0, single_walk=False, pairs=None):
+        """Returns (total, pairs[:min(total, capacity)]).  single_walk=True: the reference's own
+        protocol -- one walk per query, rows appended through a counter in ARBITRARY order
+        (collision.cl:202-215); otherwise count -> scan -> write in the deterministic order.
+        `pairs`: optional preallocated (capacity, 2) uint32 row buffer (timed loops)."""
         n = self.n
         assert coords4.shape == (n, 4) and coords4.dtype == np.float32
         radii = np.ascontiguousarray(radii, dtype=np.float32).reshape(-1)
-        pairs = np.zeros((max(capacity, 1), 2), np.uint32)
-        total = int(lib().orc_pipeline_f32(
-            _p(coords4), _p(radii), C.c_uint32(n), _p(pairs), C.c_uint64(capacity),
-            _p(self.codes), _p(self.ids), _p(self.nodes), _p(self.bounds), _p(self.flags), _p(self.offsets)))
+        if pairs is None:
+            pairs = np.zeros((max(capacity, 1), 2), np.uint32)
+        assert pairs.dtype == np.uint32 and pairs.size >= 2 * capacity
+        if single_walk:
+            total = int(lib().orc_pipeline_f32_single(
+                _p(coords4), _p(radii), C.c_uint32(n), _p(pairs), C.c_uint64(capacity),
+                _p(self.codes), _p(self.ids), _p(self.nodes), _p(self.bounds), _p(self.flags)))
+        else:
+            total = int(lib().orc_pipeline_f32(
+                _p(coords4), _p(radii), C.c_uint32(n), _p(pairs), C.c_uint64(capacity),
+                _p(self.codes), _p(self.ids), _p(self.nodes), _p(self.bounds), _p(self.flags), _p(self.offsets)))
         return total, pairs[:min(total, capacity)]
 
     @property

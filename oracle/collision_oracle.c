@@ -16,7 +16,8 @@
  * Each function cites the reference file:line it follows (paths relative to
  * the reference checkout).
  *
- * Build: gcc -O2 -fopenmp -ffp-contract=off -fno-fast-math -shared -fPIC
+ * Build: gcc -O3 -march=native -fopenmp -ffp-contract=off -fno-fast-math -shared
+ * -fPIC (oracle/Makefile; rebuilt per host CPU, see oracle/__init__.py:build).
  */
 #include <math.h>
 #include <stdint.h>
@@ -39,6 +40,16 @@ ORC_API int orc_num_threads(void) {
     return omp_get_max_threads();
 #else
     return 1;
+#endif
+}
+
+/* Launchers such as torchrun export OMP_NUM_THREADS=1; the timed baseline sets the
+ * thread count it reports explicitly. */
+ORC_API void orc_set_num_threads(int nt) {
+#ifdef _OPENMP
+    if (nt > 0) omp_set_num_threads(nt);
+#else
+    (void)nt;
 #endif
 }
 
@@ -521,6 +532,62 @@ ORC_API uint64_t orc_traverse_f32_mt(uint32_t *collisions, uint64_t capacity,
     return run;
 }
 
+/* The reference's own append protocol (collision.cl:202-215): ONE walk per query,
+ * rows appended through a shared counter, so their order is arbitrary -- exactly
+ * what upstream produces ("Need to sort, order is undefined",
+ * tests/test_collision_py.py:148).  Every thread batches its rows and reserves a
+ * block of the list with one atomic add per batch (kinder to the CPU than one
+ * atomic per row).  Timed baseline only; returns the TRUE total. */
+ORC_API uint64_t orc_traverse_f32_single(uint32_t *collisions, uint64_t capacity,
+                                         const orc_node *nodes, const float *bounds,
+                                         uint32_t n, uint32_t q_begin, uint32_t q_end) {
+    if (n < 2 || q_end <= q_begin) return 0;
+    uint64_t next = 0;
+    enum { BATCH = 4096, CHUNK = 256 };
+#pragma omp parallel
+    {
+        uint32_t *rows = (uint32_t *)malloc(sizeof(uint32_t) * 2 * BATCH);
+        uint64_t held = 0;
+#pragma omp for schedule(dynamic, 1) nowait
+        for (int64_t c = (int64_t)q_begin; c < (int64_t)q_end; c += CHUNK) {
+            const uint32_t stop = (uint32_t)(c + CHUNK < (int64_t)q_end ? c + CHUNK : q_end);
+            for (uint32_t q = (uint32_t)c; q < stop; q++) {
+                uint64_t h = traverse_one_f32(nodes, bounds, n, q, rows + held * 2, BATCH - held);
+                if (h > BATCH - held) {
+                    /* the batch could not take this query: flush, then the query goes straight to the list */
+                    uint64_t at = __atomic_fetch_add(&next, held + h, __ATOMIC_RELAXED);
+                    for (uint64_t k = 0; k < held && at + k < capacity; k++) {
+                        collisions[(at + k) * 2] = rows[k * 2];
+                        collisions[(at + k) * 2 + 1] = rows[k * 2 + 1];
+                    }
+                    at += held;
+                    held = 0;
+                    if (at < capacity) traverse_one_f32(nodes, bounds, n, q, collisions + at * 2, capacity - at);
+                } else {
+                    held += h;
+                }
+            }
+            if (held >= BATCH / 2) {
+                uint64_t at = __atomic_fetch_add(&next, held, __ATOMIC_RELAXED);
+                for (uint64_t k = 0; k < held && at + k < capacity; k++) {
+                    collisions[(at + k) * 2] = rows[k * 2];
+                    collisions[(at + k) * 2 + 1] = rows[k * 2 + 1];
+                }
+                held = 0;
+            }
+        }
+        if (held) {
+            uint64_t at = __atomic_fetch_add(&next, held, __ATOMIC_RELAXED);
+            for (uint64_t k = 0; k < held && at + k < capacity; k++) {
+                collisions[(at + k) * 2] = rows[k * 2];
+                collisions[(at + k) * 2 + 1] = rows[k * 2 + 1];
+            }
+        }
+        free(rows);
+    }
+    return next;
+}
+
 /* tests/test_collision_py.py:30-37 (find_collisions): O(N^2) box-overlap
  * brute force, independent of the tree.  Emits (i, j), i < j, row-major;
  * returns the total.  coords 4-lane slots. */
@@ -596,10 +663,9 @@ ORC_API void orc_scatter(const void *in, const void *idx, void *out, uint64_t n,
  *   codes[2n] ids[2n] nodes[2n-1] bounds[(2n-1)*8] flags[2n-1] offsets[n]
  * Returns the total pair count; stores at most `capacity` pairs in the
  * deterministic (query-major, DFS) order. */
-ORC_API uint64_t orc_pipeline_f32(const float *coords, const float *radii, uint32_t n,
-                                  uint32_t *collisions, uint64_t capacity,
-                                  uint32_t *codes, uint32_t *ids, orc_node *nodes,
-                                  float *bounds, uint32_t *flags, uint64_t *offsets) {
+static void pipeline_front_f32(const float *coords, const float *radii, uint32_t n,
+                               uint32_t *codes, uint32_t *ids, orc_node *nodes,
+                               float *bounds, uint32_t *flags) {
     float range[8];
     orc_bounds_f32x4_mt(coords, n, range);
     orc_morton_f32(codes, coords, range, n);
@@ -611,5 +677,22 @@ ORC_API uint64_t orc_pipeline_f32(const float *coords, const float *radii, uint3
     orc_generate_bvh(codes + n, nodes, n);
     orc_leaf_bounds_f32(bounds, coords, radii, nodes, n);
     orc_internal_bounds_f32(bounds, flags, nodes, n);
+}
+
+ORC_API uint64_t orc_pipeline_f32(const float *coords, const float *radii, uint32_t n,
+                                  uint32_t *collisions, uint64_t capacity,
+                                  uint32_t *codes, uint32_t *ids, orc_node *nodes,
+                                  float *bounds, uint32_t *flags, uint64_t *offsets) {
+    pipeline_front_f32(coords, radii, n, codes, ids, nodes, bounds, flags);
     return orc_traverse_f32_mt(collisions, capacity, nodes, bounds, n, offsets);
+}
+
+/* The same pipeline with the reference's single walk + counter append (rows in
+ * arbitrary order, as upstream): what bench.py times as the CPU baseline. */
+ORC_API uint64_t orc_pipeline_f32_single(const float *coords, const float *radii, uint32_t n,
+                                         uint32_t *collisions, uint64_t capacity,
+                                         uint32_t *codes, uint32_t *ids, orc_node *nodes,
+                                         float *bounds, uint32_t *flags) {
+    pipeline_front_f32(coords, radii, n, codes, ids, nodes, bounds, flags);
+    return orc_traverse_f32_single(collisions, capacity, nodes, bounds, n, 0, n);
 }

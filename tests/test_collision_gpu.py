@@ -429,3 +429,69 @@ def test_collider_two_launch_build(cuda_env, oracle):
         total, pairs = run_collider(cuda_env, col, c, r, want["total"], np.dtype("float32"))
         assert total == want["total"]
         np.testing.assert_equal(pairs, want["pairs"])
+
+
+def test_configs0_exact(cuda_env, oracle):
+    """BASELINE.json configs[0] exactly: np.random.seed(4), 1,024 spheres
+    U[0,1)^3, r = 0.01, Collider(ctx, 1024, ngroups=8, group_size=64) -- every stage and the
+    ordered list against the oracle (tests/test_collision_py.py:100-150 shape)."""
+    from collision_b200.collision import Collider
+    dev, cq = cuda_env
+    np.random.seed(4)
+    n = 1024
+    c = np.zeros((n, 4), np.float32)
+    c[:, :3] = np.random.random((n, 3)).astype('float32')
+    r = np.full(n, 0.01, np.float32)
+    want = oracle.collide(c, r)
+    assert 10 < want['total'] < 100          # ~ N^2/2 * (4r)^3 = 34
+    collider = Collider(dev, n, 8, 64)
+    assert collider.padded_size == 1024 and collider.n_nodes == 2047
+    total, pairs = run_collider(cuda_env, collider, c, r, want['total'], np.dtype('float32'))
+    np.testing.assert_equal(to_host(collider._codes_bufs[0], 'uint32', (n,)), want['codes'])
+    np.testing.assert_equal(to_host(collider._codes_bufs[1], 'uint32', (n,)), want['sorted_codes'])
+    np.testing.assert_equal(to_host(collider._ids_bufs[1], 'uint32', (n,)), want['sorted_ids'])
+    nodes = to_host(collider._nodes_buf, Node, (2 * n - 1,))
+    np.testing.assert_equal(nodes[1:]['parent'], want['nodes'][1:]['parent'])
+    np.testing.assert_equal(nodes['right_edge'], want['nodes']['right_edge'])
+    np.testing.assert_equal(nodes['data'][:n - 1], want['nodes']['data'][:n - 1])
+    np.testing.assert_equal(nodes['data'][n - 1:, 0], want['nodes']['data'][n - 1:, 0])
+    b = to_host(collider._bounds_buf, 'float32', (2 * n - 1, 2, 4))
+    np.testing.assert_equal(b[:, :, :3], want['bounds'][:, :, :3])
+    assert total == want['total']
+    np.testing.assert_equal(pairs, want['pairs'])
+    assert G.canon(pairs) == G.canon(oracle.brute_force(c, r))
+    # count-only, and the reference's own unordered contract on the Node / Bound arrays
+    total0, _ = run_collider(cuda_env, collider, c, r, 0, np.dtype('float32'))
+    assert total0 == want['total']
+    t2, p2 = run_collider(cuda_env, Collider(dev, n, 8, 64, ordered=False), c, r, want['total'], np.dtype('float32'))
+    assert t2 == total
+    np.testing.assert_equal(G.lexsorted(p2), G.lexsorted(want['pairs']))
+
+
+def test_graph_recaptured_across_resize(cuda_env, oracle):
+    """Collider(graph=True) across resize() to other sizes (re-capture on size
+    change): every size replays its own capture and returns that size's rows."""
+    import torch
+    from collision_b200.collision import Collider
+    dev, cq = cuda_env
+    col = Collider(dev, 3000, 8, 64, graph=True)
+    cap = 40000
+    n_buf = torch.zeros(1, dtype=torch.int32, device=dev)
+    pairs_d = torch.zeros(cap * 2, dtype=torch.int32, device=dev)
+    for n in (3000, 3001, 777, 3000):
+        col.resize(n)
+        rs = np.random.RandomState(n)
+        coords = np.zeros((n, 4), np.float32)
+        coords[:, :3] = rs.random_sample((n, 3))
+        radii = np.full(n, 0.03, np.float32)
+        want = oracle.collide(coords, radii)
+        coords_d, radii_d = torch.from_numpy(coords).to(dev), torch.from_numpy(radii).to(dev)
+        for rep in range(3):      # plain, capture, replay
+            pairs_d.zero_()
+            torch.cuda.synchronize()
+            col.get_collisions(cq, coords_d, radii_d, n_buf, pairs_d, cap).synchronize()
+            total = int(n_buf.item()) & 0xFFFFFFFF
+            assert total == want["total"] and total <= cap
+            got = pairs_d.cpu().numpy().view(np.uint32).reshape(-1, 2)[:total]
+            assert np.array_equal(got, want["pairs"]), (n, rep)
+        assert len(col._graphs) == 1      # the captures of the previous size were dropped with its scratch

@@ -77,7 +77,7 @@ def test_shard_range_properties():
             assert max(sizes) - min(sizes) <= 1
 
 
-def _gather_worker(rank, world, port, n, tmpdir):
+def _gather_worker(rank, world, port, n, tmpdir, raw):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     dist.init_process_group("gloo", rank=rank, world_size=world)
     try:
@@ -89,19 +89,25 @@ def _gather_worker(rank, world, port, n, tmpdir):
         radii = torch.full((n,), float("nan"), dtype=torch.float32)
         coords[b:e] = torch.from_numpy(c[b:e])
         radii[b:e] = torch.from_numpy(r[b:e].astype(np.float32))
-        gather_slices(coords, 4, n)
-        gather_slices(radii, 1, n)
-        np.save(os.path.join(tmpdir, "coords{}.npy".format(rank)), coords.numpy())
-        np.save(os.path.join(tmpdir, "radii{}.npy".format(rank)), radii.numpy())
+        if raw:     # raw-byte buffers, like every other entry point takes them
+            coords, radii = coords.view(torch.uint8).reshape(-1), radii.view(torch.uint8).reshape(-1)
+        gather_slices(coords, 16, n)
+        gather_slices(radii, 4, n)
+        np.save(os.path.join(tmpdir, "coords{}.npy".format(rank)), coords.view(torch.float32).reshape(n, 4).numpy())
+        np.save(os.path.join(tmpdir, "radii{}.npy".format(rank)), radii.view(torch.float32).numpy())
+        if rank == 0:
+            with pytest.raises(ValueError):
+                gather_slices(torch.zeros(n * 16 - 4, dtype=torch.uint8), 16, n)
     finally:
         dist.destroy_process_group()
 
 
+@pytest.mark.parametrize("raw", [False, True], ids=["typed", "raw-bytes"])
 @pytest.mark.parametrize("n", [1001, 4096])   # ragged shards (one broadcast per owner) and equal ones (all-gather)
-def test_two_rank_input_gather(tmp_path, n):
+def test_two_rank_input_gather(tmp_path, n, raw):
     """mode "gather_inputs": the scene arrives sharded by sphere index and is all-gathered in place."""
     world = 2
-    mp.spawn(_gather_worker, args=(world, _free_port(), n, str(tmp_path)), nprocs=world, join=True)
+    mp.spawn(_gather_worker, args=(world, _free_port(), n, str(tmp_path), raw), nprocs=world, join=True)
     c, r = G.random_spheres(n)
     for k in range(world):
         np.testing.assert_equal(np.load(tmp_path / "coords{}.npy".format(k)), c.astype(np.float32))

@@ -1,0 +1,145 @@
+"""ShardedCollider.get_collisions on REAL GPUs over NCCL (2 ranks, one process per GPU): every
+mode, balance=True over several frames and the CUDA-graph replay of the whole step, each rank's
+rows concatenated by pair_base and compared bit for bit with the oracle's single-rank list
+(= the reference's work-items run sequentially).  Skipped on boxes with fewer than 2 GPUs
+(`gpurun --gpus 2 -- python -m pytest tests/test_sharded_nccl_gpu.py -m gpu`)."""
+import os
+import socket
+
+import numpy as np
+import pytest
+
+import golden_data as G
+
+pytestmark = pytest.mark.gpu
+
+MODES = ("broadcast_tree", "replicate_build", "gather_inputs", "sharded_build")
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _scene(n, kind):
+    c, r = G.random_spheres(n)
+    c = np.ascontiguousarray(c, dtype=np.float32).copy()
+    if kind == "skewed":          # half the spheres packed into a corner: unequal rows per rank
+        c[: n // 2, :3] *= 0.2
+    if kind == "duplicates":      # runs of equal Morton codes straddling the rank boundary
+        c[n // 3: n // 3 + 700, :3] = c[n // 3, :3]
+    return c, np.ascontiguousarray(r, dtype=np.float32)
+
+
+def _worker(rank, world, port, n, kind, mode, balance, graph, frames, raw, tmpdir):
+    import torch
+    import torch.distributed as dist
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dev = torch.device("cuda", rank)
+    torch.cuda.set_device(dev)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    try:
+        from collision_b200.sharded import ShardedCollider, shard_range
+        c, r = _scene(n, kind)
+        b, e = shard_range(n, world, rank)
+        cq = torch.cuda.Stream(dev)
+
+        def inputs():
+            """What the rank holds before a call: everything on rank 0 for the broadcast modes,
+            its own slice of the spheres for the sharded-input modes; the rest is poison."""
+            if mode in ("gather_inputs", "sharded_build"):
+                cc, rr = np.full_like(c, np.nan), np.full_like(r, np.nan)
+                cc[b:e], rr[b:e] = c[b:e], r[b:e]
+            elif rank == 0:
+                cc, rr = c, r
+            else:
+                cc, rr = np.full_like(c, np.nan), np.full_like(r, np.nan)
+            ct, rt = torch.from_numpy(cc.copy()).to(dev), torch.from_numpy(rr.copy()).to(dev)
+            if raw:
+                ct, rt = ct.view(torch.uint8).reshape(-1), rt.view(torch.uint8).reshape(-1)
+            return ct, rt
+
+        col = ShardedCollider(dev, n, 8, 64, mode=mode, balance=balance, graph=graph)
+        n_buf = torch.zeros(1, dtype=torch.int32, device=dev)
+        ct, rt = inputs()
+        torch.cuda.synchronize()
+        col.get_collisions(cq, ct, rt, n_buf, None, 0).synchronize()          # the sizing call
+        cap = col.suggested_capacity(3.0) if balance else col.local_pairs
+        assert col.local_pairs <= cap
+        rows = torch.full((max(cap, 1) * 2,), -1, dtype=torch.int32, device=dev)
+        log = []
+        for f in range(frames):
+            ct, rt = inputs() if not graph else (ct, rt)
+            if graph and f:      # same buffers, refilled: the capture must read the new contents
+                fresh_c, fresh_r = inputs()
+                ct.copy_(fresh_c)
+                rt.copy_(fresh_r)
+            rows.fill_(-1)
+            torch.cuda.synchronize()
+            if graph:
+                col.get_collisions(cq, ct, rt, n_buf, rows, cap, sync_totals=False).synchronize()
+                totals = col._totals.tolist()
+                local, base, total = totals[rank], sum(totals[:rank]), sum(totals)
+            else:
+                col.get_collisions(cq, ct, rt, n_buf, rows, cap).synchronize()
+                assert not col.overflowed
+                local, base, total = col.local_pairs, col.pair_base, col.total_pairs
+            assert (int(n_buf.item()) & 0xFFFFFFFF) == (total & 0xFFFFFFFF)
+            got = rows.cpu().numpy().view(np.uint32).reshape(-1, 2)
+            assert (got[local:] == 0xFFFFFFFF).all()
+            np.save(os.path.join(tmpdir, "rows{}_{}.npy".format(f, rank)), got[:local])
+            log.append([local, base, total, col.q_begin, col.q_end])
+        if graph:
+            assert col.graph_replays >= frames - 2, col.graph_replays
+        np.save(os.path.join(tmpdir, "log{}.npy".format(rank)), np.array(log))
+    finally:
+        dist.destroy_process_group()
+
+
+def _run(tmp_path, oracle, n, kind, mode, balance=False, graph=False, frames=1, raw=False):
+    import torch
+    import torch.multiprocessing as mp
+    if not torch.cuda.is_available() or torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    from collision_b200.sharded import ShardedCollider
+    if mode not in ShardedCollider.MODES:
+        pytest.skip("mode {} not built".format(mode))
+    world = 2
+    mp.spawn(_worker, args=(world, _free_port(), n, kind, mode, balance, graph, frames, raw, str(tmp_path)),
+             nprocs=world, join=True)
+    c, r = _scene(n, kind)
+    want = oracle.collide(c, r)
+    logs = [np.load(tmp_path / "log{}.npy".format(k)) for k in range(world)]
+    for f in range(frames):
+        parts = [np.load(tmp_path / "rows{}_{}.npy".format(f, k)) for k in range(world)]
+        assert logs[0][f][1] == 0 and logs[1][f][1] == logs[0][f][0]          # bases = running totals
+        assert all(l[f][2] == want["total"] for l in logs)
+        assert logs[0][f][3] == 0 and logs[0][f][4] == logs[1][f][3] and logs[1][f][4] == n
+        np.testing.assert_equal(np.concatenate(parts), want["pairs"])        # rank-major == single rank, in ORDER
+    return logs
+
+
+@pytest.mark.parametrize("mode", MODES)
+@pytest.mark.parametrize("n,kind", [(20011, "uniform"), (16384, "duplicates")])
+def test_two_ranks_equal_single_rank(tmp_path, oracle, mode, n, kind):
+    _run(tmp_path, oracle, n, kind, mode)
+
+
+@pytest.mark.parametrize("mode", ["gather_inputs", "sharded_build"])
+def test_two_ranks_raw_byte_buffers(tmp_path, oracle, mode):
+    _run(tmp_path, oracle, 8192, "uniform", mode, raw=True)
+
+
+@pytest.mark.parametrize("mode", ["replicate_build", "gather_inputs", "sharded_build"])
+def test_two_ranks_balanced(tmp_path, oracle, mode):
+    logs = _run(tmp_path, oracle, 30000, "skewed", mode, balance=True, frames=4)
+    first = max(logs[0][0][0], logs[1][0][0]) / (logs[0][0][2] / 2)
+    last = max(logs[0][-1][0], logs[1][-1][0]) / (logs[0][-1][2] / 2)
+    assert first > 1.3 and last < 1.25 and last < first, (first, last)      # the re-cut evens the rows out
+    assert logs[0][-1][4] != 15000                          # ... by moving the cut
+
+
+@pytest.mark.parametrize("mode", MODES)
+def test_two_ranks_graph_replay(tmp_path, oracle, mode):
+    _run(tmp_path, oracle, 20011, "uniform", mode, graph=True, frames=4)
