@@ -23,6 +23,7 @@
 #include <cstdlib>
 
 #include "common.cuh"
+#include "sort_col.cuh"
 
 namespace {
 
@@ -370,6 +371,12 @@ int run_passes(const K* keys_in, K* keys_out, const uint32_t* vals_in, uint32_t*
         COL_CHECK_LAUNCH();
     }
     const uint32_t mask = (1u << bits) - 1;
+    // 32-bit keys take the column-counter pass (sort_col.cuh) when every buffer a pass reads is
+    // 32-byte aligned (256-bit loads); COL_SORT_LEGACY=1 forces the ballot-ranking pass (A/B timing)
+    auto aligned32 = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 31u) == 0; };
+    static const bool legacy = getenv("COL_SORT_LEGACY") != nullptr;
+    const bool col = sizeof(K) == 4 && !legacy && aligned32(keys_in) && aligned32(keys_out) && aligned32(tmp_keys) &&
+                     (!has_vals || (aligned32(vals_in) && aligned32(vals_out) && aligned32(tmp_vals)));
     for (uint32_t p = 0; p < npass; p++) {
         // the last pass lands in *_out; earlier ones alternate tmp/out backwards from there
         const bool to_out = ((npass - 1 - p) & 1u) == 0;
@@ -378,6 +385,15 @@ int run_passes(const K* keys_in, K* keys_out, const uint32_t* vals_in, uint32_t*
         const uint32_t* vin = p == 0 ? vals_in : (to_out ? tmp_vals : vals_out);
         uint32_t* vout = to_out ? vals_out : tmp_vals;
         uint32_t* status = reinterpret_cast<uint32_t*>(scratch + L.status + L.status_bytes * p);
+        if (col) {
+            const int rc = has_vals
+                ? colsort::launch<true>((const uint32_t*)kin, (uint32_t*)kout, vin, vout, n, ghist + p * RADIX, status,
+                                        tickets + p, shift0 + p * bits, mask, (unsigned)L.tiles, s)
+                : colsort::launch<false>((const uint32_t*)kin, (uint32_t*)kout, nullptr, nullptr, n, ghist + p * RADIX,
+                                         status, tickets + p, shift0 + p * bits, mask, (unsigned)L.tiles, s);
+            if (rc) return rc;
+            continue;
+        }
         if (has_vals) {
             constexpr size_t smem = onesweep_smem<K, true>();
             COL_CUDA(cudaFuncSetAttribute(onesweep_kernel<K, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
