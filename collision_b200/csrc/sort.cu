@@ -371,11 +371,14 @@ int run_passes(const K* keys_in, K* keys_out, const uint32_t* vals_in, uint32_t*
         COL_CHECK_LAUNCH();
     }
     const uint32_t mask = (1u << bits) - 1;
-    // 32-bit keys take the column-counter pass (sort_col.cuh) when every buffer a pass reads is
-    // 32-byte aligned (256-bit loads); COL_SORT_LEGACY=1 forces the ballot-ranking pass (A/B timing)
+    // COL_SORT_COLUMN=1: 32-bit keys take the column-counter pass (sort_col.cuh: ranking by counting,
+    // no votes) when every buffer a pass reads is 32-byte aligned.  Measured on B200 at 2^26 pairs it
+    // EQUALS the ballot pass (1.58 ms; both are bound by the L1/shared-memory pipe at ~25 wavefronts per
+    // row of 32 keys, ncu: profiles/r2b_ncu_sortcol_summary.txt) and is slower on sorted keys and at
+    // 2^20, so the ballot pass stays the default; the alternative is kept for A/B runs.
     auto aligned32 = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 31u) == 0; };
-    static const bool legacy = getenv("COL_SORT_LEGACY") != nullptr;
-    const bool col = sizeof(K) == 4 && !legacy && aligned32(keys_in) && aligned32(keys_out) && aligned32(tmp_keys) &&
+    static const bool column = getenv("COL_SORT_COLUMN") != nullptr;
+    const bool col = sizeof(K) == 4 && column && aligned32(keys_in) && aligned32(keys_out) && aligned32(tmp_keys) &&
                      (!has_vals || (aligned32(vals_in) && aligned32(vals_out) && aligned32(tmp_vals)));
     for (uint32_t p = 0; p < npass; p++) {
         // the last pass lands in *_out; earlier ones alternate tmp/out backwards from there

@@ -19,8 +19,8 @@
 //   * scan B: one thread per digit turns the 32 group totals of its digit into run starts
 //     inside the sorted tile (two packed 16-bit running sums), after a block scan over the
 //     digit totals, which are published for the look-back as soon as they are known;
-//   * ranking: rank = table[digit][group] + counter[digit][thread]++ -- one byte
-//     read-modify-write and one 16-bit load per key;
+//   * ranking: rank = table[digit][group] + scanned counter[digit][thread] + the key's occurrence
+//     index inside its thread (remembered from the count) -- one byte load and one 16-bit load per key;
 //   * the sorted tile (keys, or key/value pairs as 8-byte elements) re-uses the counters'
 //     64 KB, XOR-swizzled (index ^ (index >> 5)) instead of padded, and goes out in runs of
 //     consecutive addresses exactly like sort.cu.
@@ -73,7 +73,10 @@ __device__ __forceinline__ void col_tile(const uint32_t* __restrict__ keys_in, u
     unsigned char* base = smem + CNT_BYTES;          // 16-bit table, 4 x run start
     const unsigned t = threadIdx.x, lane = t & 31, warp = t >> 5;
     const unsigned b = t >> 6, x = t & 63, g = x >> 3;
-    const uint32_t toff = x * 4 + b;
+    // word x of a digit row sits at x ^ 4 for x >= 32: the two halves of groups 4..7 are swapped in
+    // memory, so that the 128-bit accesses of scan A (8 consecutive groups per quarter warp, every
+    // lane asking for the same logical half) fall on 8 different bank quads instead of 4
+    const uint32_t toff = (x ^ ((x >> 5) << 2)) * 4 + b;
     const uint32_t tile_base = tile * (uint32_t)TILE;
     const uint32_t valid = FULL ? (uint32_t)TILE : n - tile_base;
 
@@ -90,39 +93,41 @@ __device__ __forceinline__ void col_tile(const uint32_t* __restrict__ keys_in, u
         }
     }
 
-    // ---- count: one byte per (digit, thread); program order per thread, no atomics
+    // ---- count: one byte per (digit, thread); program order per thread, no atomics.  What the
+    // counter held before a key's increment is the number of EARLIER keys of this thread with the
+    // same digit: kept (a byte per key, four per register) so that the ranking needs no second
+    // read-modify-write
+    uint32_t occ[I / 4];
 #pragma unroll
-    for (int i = 0; i < I; i++) {
-        unsigned char* p = cnt + cnt_addr<BYTE>(key[i], toff, shift, mask);
-        *p = (unsigned char)(*p + 1);
-    }
-    // payload loads are issued here so that their latency hides behind the scans
-    uint32_t val[HAS_VALUES ? I : 1];
-    if (HAS_VALUES) {
-        const uint32_t* src = vals_in + tile_base + t * I;
-        if (FULL) {
+    for (int i = 0; i < I; i += 4) {
+        uint32_t q4 = 0;
 #pragma unroll
-            for (int v = 0; v < I / 8; v++) ld_v8(src + v * 8, val + v * 8);
-        } else {
-#pragma unroll
-            for (int i = 0; i < I; i++) val[i] = (t * I + i) < valid ? src[i] : 0u;
+        for (int h = 0; h < 4; h++) {
+            unsigned char* p = cnt + cnt_addr<BYTE>(key[i + h], toff, shift, mask);
+            const uint32_t q = *p;
+            *p = (unsigned char)(q + 1);
+            q4 |= q << (8 * h);
         }
+        occ[i >> 2] = q4;
     }
     __syncthreads();
 
     // ---- scan A: unit u = (digit u >> 3, group u & 7) = 8 words = the counters of 8 consecutive
     // threads x 4 byte lanes.  Exclusive prefix over the 8 words by packed adds (<= 224 per byte),
     // the group's four totals (<= 256 each, hence summed in two halves) to the 16-bit table.
+    const unsigned flip = (t >> 2) & 1u;             // group (u & 7) >= 4: its halves are swapped (see toff)
 #pragma unroll
     for (int k = 0; k < (NDIG * 8) / T; k++) {
         const unsigned u = t + T * k;
         uint4* p = reinterpret_cast<uint4*>(cnt + u * 32);
-        const uint4 a = p[0], c = p[1];
+        uint4* pa = p + flip;                        // threads 0..3 of the group
+        uint4* pc = p + (flip ^ 1u);                 // threads 4..7
+        const uint4 a = *pa, c = *pc;
         const uint32_t e1 = a.x, e2 = e1 + a.y, e3 = e2 + a.z, e4 = e3 + a.w;
         const uint32_t e5 = e4 + c.x, e6 = e5 + c.y, e7 = e6 + c.z;
         const uint32_t thi = e7 - e4 + c.w;          // threads 4..7 of the group, per byte lane
-        p[0] = make_uint4(0u, e1, e2, e3);
-        p[1] = make_uint4(e4, e5, e6, e7);
+        *pa = make_uint4(0u, e1, e2, e3);
+        *pc = make_uint4(e4, e5, e6, e7);
         const uint32_t A = (e4 & 0x00ff00ffu) + (thi & 0x00ff00ffu);                    // lanes b0 | b2 << 16
         const uint32_t Bv = ((e4 >> 8) & 0x00ff00ffu) + ((thi >> 8) & 0x00ff00ffu);     // lanes b1 | b3 << 16
         *reinterpret_cast<uint2*>(base + (u >> 3) * BASE_ROW + (u & 7) * 8) = make_uint2(A, Bv);
@@ -166,8 +171,23 @@ __device__ __forceinline__ void col_tile(const uint32_t* __restrict__ keys_in, u
     }
     __syncthreads();
 
-    // ---- rank: slot = table[digit][my group] + counter[digit][me]++ ; kept as the swizzled byte
-    // offset of the slot (x 2 for key/value pairs), two per register
+    // payload loads are issued here: their latency hides behind the ranking, and their 32 registers
+    // are not held through the count and the scans
+    uint32_t val[HAS_VALUES ? I : 1];
+    if (HAS_VALUES) {
+        const uint32_t* src = vals_in + tile_base + t * I;
+        if (FULL) {
+#pragma unroll
+            for (int v = 0; v < I / 8; v++) ld_v8(src + v * 8, val + v * 8);
+        } else {
+#pragma unroll
+            for (int i = 0; i < I; i++) val[i] = (t * I + i) < valid ? src[i] : 0u;
+        }
+    }
+
+    // ---- rank: slot = table[digit][my group] + (threads of my group before me: the scanned
+    // counter) + (my earlier keys: occ); kept as the swizzled byte offset of the slot (x 2 for
+    // key/value pairs), two per register
     uint32_t rk[I / 2];
     {
         // entry of (b, g) inside a row: word g * 2 + (b & 1), half b >> 1
@@ -178,9 +198,7 @@ __device__ __forceinline__ void col_tile(const uint32_t* __restrict__ keys_in, u
 #pragma unroll
             for (int h = 0; h < 2; h++) {
                 const uint32_t a = cnt_addr<BYTE>(key[i + h], toff, shift, mask);
-                unsigned char* p = cnt + a;
-                const uint32_t q = *p;
-                *p = (unsigned char)(q + 1);
+                const uint32_t q = (uint32_t)cnt[a] + ((occ[(i + h) >> 2] >> (8 * ((i + h) & 3))) & 0xffu);
                 const uint32_t d = digit_of<BYTE>(key[i + h], shift, mask);
                 const uint32_t bs4 = *reinterpret_cast<const uint16_t*>(base + d * BASE_ROW + boff);
                 const uint32_t r4 = bs4 + (q << 2);

@@ -186,69 +186,26 @@ count_kernel(unsigned long long* __restrict__ total, uint32_t* __restrict__ coun
 // array stash[k * nq + i]: lanes of a warp park their k-th candidate in one 128-byte row,
 // and only rows that are actually used ever move.  No inter-block dependency, so dense
 // and sparse regions of the scene do not stall each other.
-// Lanes of a warp finish their walks at different times (ncu, one query per lane: 18 of 32 lanes
-// active on average -- the warp runs as long as its longest walk).  Every lane therefore takes
-// TRV_QPL queries, 32 apart, one after the other: the warp's time becomes the longest SUM of
-// TRV_QPL walks, whose relative spread is about 1/sqrt(TRV_QPL) of a single walk's.  The walk on the
-// records needs only the query's grid image (3 registers), so all TRV_QPL of them are prepared up
-// front with their box loads in flight together: moving on to the next query costs no memory latency.
-#ifndef COL_TRV_QPL
-#define COL_TRV_QPL 4
-#endif
-constexpr int TRV_QPL = COL_TRV_QPL;
-
 template <typename T>
 __global__ void __launch_bounds__(TRV_THREADS)
 candidates_kernel(uint32_t* __restrict__ counts, uint32_t* __restrict__ stash, const unsigned char* __restrict__ wide,
                   const T* __restrict__ bounds, const T* __restrict__ scene, uint32_t n, uint32_t q_begin,
                   uint32_t q_end, uint32_t prefetch_lines, uint32_t depth) {
     const uint32_t nq = q_end - q_begin;
-    const uint32_t block_first = blockIdx.x * (TRV_THREADS * TRV_QPL);
+    const uint32_t i = blockIdx.x * TRV_THREADS + threadIdx.x;
     {   // the low levels of the walks of this block live in the records right of its first query
-        const uint32_t first = q_begin + block_first;
+        const uint32_t first = q_begin + blockIdx.x * TRV_THREADS;
         const uint32_t rec = first + threadIdx.x * 4;  // one 128-byte line (4 records) per thread
         if (threadIdx.x < prefetch_lines && rec < n - 1)
             asm volatile("prefetch.global.L1 [%0];" ::"l"(wide + (size_t)rec * QNODE_BYTES));
     }
-    // query j of this lane: warp w of the block owns queries [w * 32 * QPL, (w + 1) * 32 * QPL), lane l takes l + 32 j
-    const uint32_t i0 = block_first + (threadIdx.x >> 5) * (32 * TRV_QPL) + lane_id();
-    if (i0 >= nq) return;
-    const uint32_t leaf_start = n - 1;
-    uint3 grid[TRV_QPL];
-    {
-        const Quant<T> qz = make_quant(scene);
-        LeafBox<T> box[TRV_QPL];
-#pragma unroll
-        for (int j = 0; j < TRV_QPL; j++)
-            if (i0 + 32 * j < nq) box[j] = load_leaf_box(bounds, leaf_start + q_begin + i0 + 32 * j);
-#pragma unroll
-        for (int j = 0; j < TRV_QPL; j++)
-            grid[j] = i0 + 32 * j < nq ? quantise_query(qz, box[j].lo, box[j].hi) : make_uint3(0u, 0u, 0u);
-    }
-    uint32_t stack[64];
-    Query<T> query;      // (only .grid is read by the walk on the records)
-#pragma unroll 1
-    for (int j = 0; j < TRV_QPL; j++) {
-        const uint32_t i = i0 + 32 * j;
-        if (i >= nq) break;
-        const uint32_t q = q_begin + i;
-        // (a switch, not an indexed read: grid[] stays in registers)
-        query.grid = j == 0 ? grid[0] : j == 1 ? grid[1 % TRV_QPL] : j == 2 ? grid[2 % TRV_QPL] : grid[3 % TRV_QPL];
-        uint32_t hits = 0;
-        if (q < leaf_start) {   // the last sorted leaf has nothing to its right
-            uint32_t* park = stash + i;
-            int sp = 0;
-            stack[sp++] = TRV_DONE;
-            uint32_t idx = 0;
-            do {
-                idx = visit<false>(wide, bounds, query, q, leaf_start, idx, stack, sp, [&](uint32_t pos, bool valid) {
-                    if (valid && hits < depth) park[(size_t)hits * nq] = pos;
-                    hits += valid ? 1u : 0u;
-                });
-            } while (idx != TRV_DONE);
-        }
-        counts[i] = hits;
-    }
+    if (i >= nq) return;
+    const uint32_t q = q_begin + i, leaf_start = n - 1;
+    const Query<T> query = load_query(bounds, leaf_start + q, make_quant(scene));
+    uint32_t* park = stash + i;
+    counts[i] = walk<false>(wide, bounds, query, q, leaf_start, [park, nq, depth](uint32_t pos, uint32_t k, bool valid) {
+        if (valid && k < depth) park[(size_t)k * nq] = pos;
+    });
 }
 
 // ---- confirm: candidates -> collision rows ----------------------------------------
@@ -471,8 +428,11 @@ static int pairs_impl(uint32_t* pairs, uint64_t capacity, uint64_t base, unsigne
     uint32_t* stash = reinterpret_cast<uint32_t*>(sc + L.stash);
     const unsigned blocks = col_blocks(nq, TRV_THREADS);
     const uint32_t pf = 64;   // 128-byte lines of the block's own record window prefetched to L1 (0..256: +4 % at 64)
-    static_assert(TRV_QPL >= 1 && TRV_QPL <= 4, "candidates_kernel selects among at most 4 prepared queries");
-    candidates_kernel<T><<<col_blocks(nq, TRV_THREADS * TRV_QPL), TRV_THREADS, 0, s>>>(counts, stash, w, bounds, scene, n, q_begin, q_end, pf, depth);
+    // (Round 2, measured and dropped -- profiles/r2e_traversal_variants.txt: walk + confirmation fused into
+    //  one launch, 7.84 vs 7.48 ms at configs[3]; four queries per lane in the walk, 12.4 ms; four leaf boxes
+    //  in flight per lane in the confirmation, 2.25 vs 1.99 ms; an emit that builds whole rows per window of
+    //  the warp's strip, 2.13 vs 1.70 ms.)
+    candidates_kernel<T><<<blocks, TRV_THREADS, 0, s>>>(counts, stash, w, bounds, scene, n, q_begin, q_end, pf, depth);
     COL_CHECK_LAUNCH();
     COL_CUDA((cudaError_t)mark(0));
     confirm_kernel<T><<<blocks, TRV_THREADS, 0, s>>>(total, counts, stash, w, bounds, scene, n, q_begin, q_end, depth);

@@ -27,15 +27,21 @@ def tile_pass(keys, shift, mask, valid=None):
     dig = (keys >> shift) & mask
     cnt = np.zeros(65536, np.uint8)            # byte c[d][t] at d*256 + (t&63)*4 + (t>>6)
     t_idx = np.repeat(np.arange(T), I)
-    toff = (t_idx & 63) * 4 + (t_idx >> 6)
+    xs = t_idx & 63
+    toff = (xs ^ ((xs >> 5) << 2)) * 4 + (t_idx >> 6)      # halves of groups 4..7 swapped in memory
     # count phase (sequential per thread; numpy: accumulate)
-    np.add.at(cnt, dig.astype(np.int64) * 256 + toff, 1)
+    occ = np.zeros(TILE, np.int64)              # counter value before the key's own increment
+    for idx in range(TILE):
+        a = int(dig[idx]) * 256 + int(toff[idx])
+        occ[idx] = cnt[a]
+        cnt[a] += 1
     # scan A: unit u = d*8+g, 8 words
     words = cnt.view(np.uint32).copy()
     base = np.zeros(256 * ROW // 2, np.uint16)     # u16 entries, row stride 40 entries
     for u in range(2048):
         d, g = u >> 3, u & 7
-        w = words[u * 8:u * 8 + 8].astype(np.uint64)
+        flip = (g >> 2) & 1
+        w = np.concatenate([words[u * 8 + 4 * flip:u * 8 + 4 * flip + 4], words[u * 8 + 4 * (flip ^ 1):u * 8 + 4 * (flip ^ 1) + 4]]).astype(np.uint64)
         e = np.zeros(8, np.uint64)
         for j in range(1, 8):
             e[j] = (e[j - 1] + w[j - 1]) & 0xFFFFFFFF
@@ -44,7 +50,8 @@ def tile_pass(keys, shift, mask, valid=None):
         thi = (w[4] + w[5] + w[6] + w[7]) & 0xFFFFFFFF
         A = (tlo & 0x00ff00ff) + (thi & 0x00ff00ff)
         B = ((tlo >> 8) & 0x00ff00ff) + ((thi >> 8) & 0x00ff00ff)
-        words[u * 8:u * 8 + 8] = e.astype(np.uint32)
+        words[u * 8 + 4 * flip:u * 8 + 4 * flip + 4] = e[:4].astype(np.uint32)
+        words[u * 8 + 4 * (flip ^ 1):u * 8 + 4 * (flip ^ 1) + 4] = e[4:].astype(np.uint32)
         ent = d * (ROW // 2) + g * 4
         base[ent + 0] = A & 0xffff
         base[ent + 1] = A >> 16
@@ -76,9 +83,8 @@ def tile_pass(keys, shift, mask, valid=None):
         for i in range(I):
             k = keys[t * I + i]
             d = int((k >> shift) & mask)
-            a = d * 256 + x * 4 + b
-            q = int(cnt[a])
-            cnt[a] = (q + 1) & 0xff
+            a = d * 256 + (x ^ ((x >> 5) << 2)) * 4 + b
+            q = int(cnt[a]) + int(occ[t * I + i])
             r4 = int(base4[d * (ROW // 2) + g * 4 + perm(b)]) + (q << 2)
             r = r4 >> 2
             phys[t * I + i] = swz(r)
