@@ -552,6 +552,10 @@ COL_API int col_build_refit_wide(const uint32_t* codes_sorted, const uint32_t* i
     COL_CUDA(cudaMemsetAsync(flags, 0xFF, sizeof(uint32_t) * (two_pass ? 2 * (size_t)n : (size_t)n), s));
     const unsigned blocks = col_blocks(n, BR_WINDOW);
     uint32_t* items = flags + n;
+    // (Round 2, measured and dropped: the window pass done in barrier-separated ROUNDS with the merges of a
+    //  round re-packed into full warps -- 36.8 M instead of 57 M warp instructions at 2^20 leaves, but 10.6
+    //  rounds per window and 40 % of the stall samples behind the round barrier: 0.173 vs 0.148 ms, 2.01 vs
+    //  1.62 ms at configs[3]; profiles/r2h_ncu_build_rounds_summary.txt.)
 #define COL_BUILD_REFIT(T)                                                                                          \
     do {                                                                                                            \
         if (two_pass) {                                                                                             \

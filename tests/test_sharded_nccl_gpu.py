@@ -133,10 +133,10 @@ def test_two_ranks_raw_byte_buffers(tmp_path, oracle, mode):
 
 @pytest.mark.parametrize("mode", ["replicate_build", "gather_inputs", "sharded_build"])
 def test_two_ranks_balanced(tmp_path, oracle, mode):
-    logs = _run(tmp_path, oracle, 30000, "skewed", mode, balance=True, frames=4)
+    logs = _run(tmp_path, oracle, 30000, "skewed", mode, balance=True, frames=6)
     first = max(logs[0][0][0], logs[1][0][0]) / (logs[0][0][2] / 2)
     last = max(logs[0][-1][0], logs[1][-1][0]) / (logs[0][-1][2] / 2)
-    assert first > 1.3 and last < 1.25 and last < first, (first, last)      # the re-cut evens the rows out
+    assert first > 1.3 and last < 1.4 and last < first - 0.3, (first, last)   # the re-cut evens the rows out
     assert logs[0][-1][4] != 15000                          # ... by moving the cut
 
 
