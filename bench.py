@@ -638,6 +638,15 @@ def run_single(args):
     print(json.dumps(line), flush=True)
 
 
+_T0 = time.perf_counter()
+
+
+def crumb(what):
+    """Progress marks on stderr (rank 0): where a long multi-GPU run spends its wall clock."""
+    if int(os.environ.get("RANK", "0")) == 0:
+        print("[bench +{:6.1f}s] {}".format(time.perf_counter() - _T0, what), file=sys.stderr, flush=True)
+
+
 def run_multi(args):
     import datetime
 
@@ -678,6 +687,7 @@ def run_multi(args):
         return c, torch.full((n,), float(radius_for(n)), device=dev)
 
     def measure(n, seed, steps, with_e2e, with_parity):
+        crumb("scene n={}".format(n))
         full_c, full_r = device_scene(n, seed)
         b, e = shard_range(n, world, rank)
         mine_pin_c = full_c[b:e].cpu().pin_memory()
@@ -692,6 +702,7 @@ def run_multi(args):
         else:
             coords_d, radii_d = (full_c.clone(), full_r.clone()) if rank == 0 else \
                 (torch.full_like(full_c, float("nan")), torch.full_like(full_r, float("nan")))
+        crumb("collider + count-only call")
         col = ShardedCollider(dev, n, 8, 128, mode=mode, graph=not args.no_graph)
         n_buf = torch.zeros(1, dtype=torch.int32, device=dev)
         cq.wait_stream(torch.cuda.current_stream())
@@ -706,6 +717,7 @@ def run_multi(args):
             flush.fill_(0)
             step()
             torch.cuda.synchronize()
+        crumb("timed steps")
         launches0 = col.kernel_launches
         ms = time_steps(torch, cq, flush, step, steps, barrier)
         launches = col.kernel_launches - launches0
@@ -717,6 +729,7 @@ def run_multi(args):
         assert (int(n_buf.item()) & 0xFFFFFFFF) == (total & 0xFFFFFFFF)
 
         if with_e2e:
+            crumb("e2e")
             pin_rows = torch.empty(max(cap, 1) * 2, dtype=torch.int32).pin_memory()
             n_pin = torch.zeros(1, dtype=torch.int32).pin_memory()
 
@@ -749,6 +762,7 @@ def run_multi(args):
             del pin_rows
 
         if with_parity:
+            crumb("parity check")
             # every rank's rows against the matching slice of the 1-GPU list (rank 0 runs the
             # single-GPU Collider on the same scene, outside every timed region)
             mine = torch.tensor([rows_checksum(pairs_d[:cap * 2].view(torch.int64), col.pair_base, torch) - (1 << 63),
@@ -782,6 +796,7 @@ def run_multi(args):
         torch.cuda.empty_cache()
         return res
 
+    crumb("process group up")
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
@@ -853,6 +868,7 @@ def run_multi(args):
                 "stages_ms": weak_stages, "parity_check": {"rows_equal_single_gpu": weak["parity"], "mode": mode}},
         }
         print(json.dumps(line), flush=True)
+    crumb("done")
     ok = R["parity"] and (weak is None or weak["parity"])
     dist.barrier()
     dist.destroy_process_group()
