@@ -163,9 +163,42 @@ def device_of(ctx):
     return dev
 
 
+_DEBUG = _os.environ.get("COL_B200_DEBUG") == "1"
+_GUARD = 4096            # bytes of canary before and after every scratch buffer of a debug run
+_guarded = []            # weak references to the guarded allocations
+
+
 def alloc_bytes(ctx, nbytes):
-    """Private scratch (the reference's HOST_NO_ACCESS cl.Buffer)."""
-    return torch.empty(max(int(nbytes), 1), dtype=torch.uint8, device=ctx)
+    """Private scratch (the reference's HOST_NO_ACCESS cl.Buffer).  With COL_B200_DEBUG=1 every
+    buffer sits between two 4 KB canaries that check_canaries() verifies (compute-sanitizer is
+    not available on every pool; this catches out-of-bounds writes of the kernels' scratch)."""
+    n = max(int(nbytes), 1)
+    if not _DEBUG:
+        return torch.empty(n, dtype=torch.uint8, device=ctx)
+    import weakref
+    whole = torch.empty(n + 2 * _GUARD, dtype=torch.uint8, device=ctx)
+    whole[:_GUARD].fill_(0xA5)
+    whole[_GUARD + n:].fill_(0xA5)
+    _guarded.append(weakref.ref(whole))
+    view = whole[_GUARD:_GUARD + n]
+    view._col_whole = whole        # keeps the canaries alive as long as the view is
+    return view
+
+
+def check_canaries():
+    """Debug runs: every live scratch buffer's canaries are intact.  Returns how many were checked."""
+    torch.cuda.synchronize()
+    live = 0
+    for ref in list(_guarded):
+        whole = ref()
+        if whole is None:
+            _guarded.remove(ref)
+            continue
+        live += 1
+        if not (bool((whole[:_GUARD] == 0xA5).all()) and bool((whole[-_GUARD:] == 0xA5).all())):
+            raise CollisionLibraryError("scratch canary overwritten: a kernel wrote outside its buffer "
+                                        "({} bytes allocation)".format(whole.numel() - 2 * _GUARD))
+    return live
 
 
 def alloc_on(cq, ctx, nbytes):

@@ -251,6 +251,9 @@ __device__ __forceinline__ uint32_t finish_node(col_node* __restrict__ nodes, un
     const bool root = lo == 0 && hi == leaf_start;
     const uint32_t idx = root ? 0u : (dr > dl ? hi : lo);  // Karras: a left child is numbered by its hi, a right child by its lo
     const uint32_t child_a = is_left ? self : sibling, child_b = is_left ? sibling : self;
+#ifdef COL_DEBUG
+    if (lo > hi || hi > leaf_start || idx >= leaf_start || child_a > 2 * leaf_start || child_b > 2 * leaf_start) __trap();
+#endif
     {
         uint32_t* rec = reinterpret_cast<uint32_t*>(nodes + idx);
         rec[1] = hi;
@@ -428,6 +431,9 @@ build_refit_kernel(const uint32_t* __restrict__ codes, const uint32_t* __restric
         const bool root = lo == 0 && hi == leaf_start;
         const uint32_t idx = root ? 0u : (dr > dl ? hi : lo);  // Karras: a left child is numbered by its hi, a right child by its lo
         const uint32_t child_a = is_left ? self : sibling, child_b = is_left ? sibling : self;
+#ifdef COL_DEBUG   // a torn hand-over (far end read before it was written) shows up as an impossible range or index
+        if (lo > hi || hi > leaf_start || idx >= leaf_start || child_a > 2 * leaf_start || child_b > 2 * leaf_start) __trap();
+#endif
         {
             uint32_t* rec = reinterpret_cast<uint32_t*>(nodes + idx);
             rec[1] = hi;

@@ -282,6 +282,9 @@ __device__ __forceinline__ void onesweep_tile(const K* __restrict__ keys_in, K* 
             const K k = s_keys[skewed(pos)];
             const uint32_t d = (uint32_t)(k >> shift) & mask;
             const uint32_t dst = s_global_off[d] + pos;
+#ifdef COL_DEBUG   // a wrong look-back sum or digit base shows up as a destination outside the array
+            if (dst >= n) __trap();
+#endif
             keys_out[dst] = k;
             if (HAS_VALUES) vals_out[dst] = s_vals[skewed(pos)];
         }

@@ -258,6 +258,9 @@ __device__ __forceinline__ void col_tile(const uint32_t* __restrict__ keys_in, u
                 k = *reinterpret_cast<const uint32_t*>(cnt + sw * 4);
             }
             const uint32_t dst = s_goff[digit_of<BYTE>(k, shift, mask)] + pos;
+#ifdef COL_DEBUG
+            if (dst >= n) __trap();
+#endif
             keys_out[dst] = k;
             if (HAS_VALUES) vals_out[dst] = v;
         }

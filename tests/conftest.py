@@ -30,3 +30,14 @@ def cuda_env():
     dev = torch.device("cuda", 0)
     torch.cuda.set_device(dev)
     return dev, torch.cuda.Stream(dev)
+
+
+@pytest.fixture(autouse=True)
+def scratch_canaries():
+    """COL_B200_DEBUG=1 (the -DCOL_DEBUG library: index / stack-depth traps in the kernels): after every
+    test the canaries around each scratch buffer the package allocated are checked."""
+    yield
+    import os
+    if os.environ.get("COL_B200_DEBUG") == "1":
+        from collision_b200 import _lib
+        _lib.check_canaries()
