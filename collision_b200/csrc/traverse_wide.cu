@@ -213,11 +213,14 @@ candidates_kernel(uint32_t* __restrict__ counts, uint32_t* __restrict__ stash, c
 // its parked candidates (coalesced k-major rows), keeps the confirmed ones in place (same
 // order) and replaces counts[i] by the number of rows of the query.  A query with more
 // than `depth` candidates walks again, exactly, parking its first `depth` rows.
+// What is kept is the partner's ID, not its position: ids[position] is fetched beside the leaf
+// box (both depend on the position only, so the gather adds no link to the dependent chain here),
+// and the emit kernel, whose chain was stash -> ids -> strip, copies what it finds.
 template <typename T>
 __global__ void __launch_bounds__(TRV_THREADS)
 confirm_kernel(unsigned long long* __restrict__ total, uint32_t* __restrict__ counts, uint32_t* __restrict__ stash,
                const unsigned char* __restrict__ wide, const T* __restrict__ bounds, const T* __restrict__ scene,
-               uint32_t n, uint32_t q_begin, uint32_t q_end, uint32_t depth) {
+               const uint32_t* __restrict__ ids, uint32_t n, uint32_t q_begin, uint32_t q_end, uint32_t depth) {
     const uint32_t nq = q_end - q_begin;
     const uint32_t i = blockIdx.x * TRV_THREADS + threadIdx.x;
     uint32_t hits = 0;
@@ -233,25 +236,34 @@ confirm_kernel(unsigned long long* __restrict__ total, uint32_t* __restrict__ co
                 for (int k = 0; k < 3; k++) { query.lo[k] = b.lo[k]; query.hi[k] = b.hi[k]; }
                 // software pipeline: position k+2 and box k+1 are in flight while box k is tested (the
                 // compaction writes slot hits <= k, behind every slot still to be read)
-                uint32_t p0 = park[0], p1 = cand > 1 ? park[nq] : 0u;
-                LeafBox<T> b0 = load_leaf_box(bounds, leaf_start + p0);
+                uint32_t p1 = cand > 1 ? park[nq] : 0u;
+                uint32_t id0;
+                LeafBox<T> b0;
+                {
+                    const uint32_t p0 = park[0];
+                    b0 = load_leaf_box(bounds, leaf_start + p0);
+                    id0 = __ldg(ids + p0);
+                }
                 for (uint32_t k = 0; k < cand; k++) {
                     LeafBox<T> b1 = b0;
-                    uint32_t p2 = 0;
-                    if (k + 1 < cand) b1 = load_leaf_box(bounds, leaf_start + p1);
+                    uint32_t p2 = 0, id1 = 0;
+                    if (k + 1 < cand) {
+                        b1 = load_leaf_box(bounds, leaf_start + p1);
+                        id1 = __ldg(ids + p1);
+                    }
                     if (k + 2 < cand) p2 = park[(size_t)(k + 2) * nq];
                     if (exact_overlap(query, b0)) {
-                        park[(size_t)hits * nq] = p0;
+                        park[(size_t)hits * nq] = id0;
                         hits++;
                     }
-                    p0 = p1;
+                    id0 = id1;
                     p1 = p2;
                     b0 = b1;
                 }
             } else {
                 const Query<T> query = load_query(bounds, leaf_start + q, make_quant(scene));
-                hits = walk<true>(wide, bounds, query, q, leaf_start, [park, nq, depth](uint32_t pos, uint32_t k, bool) {
-                    if (k < depth) park[(size_t)k * nq] = pos;
+                hits = walk<true>(wide, bounds, query, q, leaf_start, [park, nq, depth, ids](uint32_t pos, uint32_t k, bool) {
+                    if (k < depth) park[(size_t)k * nq] = __ldg(ids + pos);
                 });
             }
             counts[i] = hits;
@@ -306,14 +318,11 @@ emit_kernel(uint32_t* __restrict__ pairs, uint64_t capacity, uint64_t base, cons
         }
         const uint32_t rows = __shfl_sync(0xffffffffu, start, 31);
         start -= mine;
-        {   // all loads of the round in flight together: positions, then ids, then the strip
-            uint32_t pos[EMIT_CHUNK], other[EMIT_CHUNK];
+        {   // all loads of the round in flight together (the stash holds partner ids: see confirm_kernel)
+            uint32_t other[EMIT_CHUNK];
 #pragma unroll
             for (uint32_t k = 0; k < EMIT_CHUNK; k++)
-                if (k < mine) pos[k] = __ldg(stash + (size_t)(k0 + k) * nq + i);
-#pragma unroll
-            for (uint32_t k = 0; k < EMIT_CHUNK; k++)
-                if (k < mine) other[k] = __ldg(ids + pos[k]);
+                if (k < mine) other[k] = __ldg(stash + (size_t)(k0 + k) * nq + i);
 #pragma unroll
             for (uint32_t k = 0; k < EMIT_CHUNK; k++)
                 if (k < mine) {
@@ -435,7 +444,7 @@ static int pairs_impl(uint32_t* pairs, uint64_t capacity, uint64_t base, unsigne
     candidates_kernel<T><<<blocks, TRV_THREADS, 0, s>>>(counts, stash, w, bounds, scene, n, q_begin, q_end, pf, depth);
     COL_CHECK_LAUNCH();
     COL_CUDA((cudaError_t)mark(0));
-    confirm_kernel<T><<<blocks, TRV_THREADS, 0, s>>>(total, counts, stash, w, bounds, scene, n, q_begin, q_end, depth);
+    confirm_kernel<T><<<blocks, TRV_THREADS, 0, s>>>(total, counts, stash, w, bounds, scene, ids, n, q_begin, q_end, depth);
     COL_CHECK_LAUNCH();
     COL_CUDA((cudaError_t)mark(1));
     const int rc = col_exclusive_scan_u32(counts, nq, nullptr, sc + L.scan, stream);
