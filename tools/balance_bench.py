@@ -1,6 +1,6 @@
 """ShardedCollider(balance=True) on a skewed scene, frame after frame (run under torchrun, >= 2 GPUs):
     python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 \
-        tools/balance_bench.py [--n 4194304] [--frames 6]
+        tools/balance_bench.py [--spheres 4194304] [--frames 6]
 Half the spheres sit in a few dense clusters, half are spread out, so equal query counts per rank mean
 unequal rows.  Every frame prints the cut, the rows per rank and the step time (max over ranks, CUDA
 events); the rows of all ranks together are checked against the first frame's count."""
@@ -32,16 +32,24 @@ def skewed_scene(n, dev, seed=4):
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--n", type=int, default=1 << 22)
+    ap.add_argument("--spheres", dest="n", type=int, default=1 << 22)
     ap.add_argument("--frames", type=int, default=6)
     ap.add_argument("--mode", default="replicate_build")
+    ap.add_argument("--scene", choices=["skewed", "configs3"], default="skewed",
+                    help="configs3: BASELINE.json configs[3], 1024 Gaussian clusters (use --spheres 16777216)")
     args = ap.parse_args()
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
     dev = torch.device("cuda", int(os.environ.get("LOCAL_RANK", "0")))
     torch.cuda.set_device(dev)
     dist.init_process_group("nccl", device_id=dev, timeout=datetime.timedelta(seconds=120))
     n = args.n
-    coords, radii = skewed_scene(n, dev)          # same seed on every rank: identical scene
+    if args.scene == "configs3":                  # the host generator of bench.py / the full-size test: identical on every rank
+        sys.path.insert(0, str(ROOT))
+        from bench import clustered_scene
+        c, r = clustered_scene(n)
+        coords, radii = torch.from_numpy(c).to(dev), torch.from_numpy(r).to(dev)
+    else:
+        coords, radii = skewed_scene(n, dev)      # same seed on every rank: identical scene
     cq = torch.cuda.Stream(dev)
     n_buf = torch.zeros(1, dtype=torch.int32, device=dev)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
@@ -72,7 +80,8 @@ def main():
             assert sum(rows) == total and max(rows) <= cap, (rows, total, cap)
             if rank == 0:
                 print("balance={} frame {} step {:.3f} ms  rows/rank {}  max/mean {:.2f}  cut {}".format(
-                    balance, frame, float(ms.item()), rows, max(rows) * world / max(total, 1), edges), flush=True)
+                    balance, frame, float(ms.item()), rows, max(rows) * world / max(total, 1),
+                    edges if world <= 4 else "..."), flush=True)
     dist.destroy_process_group()
 
 
