@@ -58,6 +58,16 @@ SIGNATURES = {
     "col_compat_find_offsets": (_int, [_vp, _u64, _u32, _vp, _u32, _vp]),
     "col_compat_reduce1": (_int, [_vp, _u64, _int, _u32, _vp, _vp, _u32, _vp, _u32, _u32, _vp]),
     "col_compat_reduce2": (_int, [_vp, _vp, _int, _u32, _vp, _u32, _u32, _vp]),
+    "col_ipc_alloc": (_int, [_vp, _u64]),
+    "col_ipc_free": (_int, [_vp]),
+    "col_ipc_export": (_int, [_vp, _vp]),
+    "col_ipc_open": (_int, [_vp, _vp]),
+    "col_ipc_close": (_int, [_vp]),
+    "col_shard_packed_bytes": (_sz, [_u32, _int]),
+    "col_shard_list_bytes": (_sz, [_u32]),
+    "col_shard_build_windows": (_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _int, _u32, _u32, _u32, _vp, _u32, _vp]),
+    "col_shard_top": (_int, [_vp, _u32, _u32, _u32, _vp, _vp, _vp, _vp, _vp, _vp, _int, _u32, _vp]),
+    "col_shard_halo": (_int, [_vp, _u32, _u32, _u32, _vp, _vp, _vp, _int, _vp, _vp, _u32, _vp, _vp, _vp, _u32, _u32, _u32, _vp]),
     "col_fill_u32": (_int, [_vp, _u32, _u64, _vp]),
     "col_range": (_int, [_vp, _u64, _vp]),
     "col_copy": (_int, [_vp, _vp, _u64, _vp]),

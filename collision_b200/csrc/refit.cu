@@ -326,13 +326,13 @@ build_refit_kernel(const uint32_t* __restrict__ codes, const uint32_t* __restric
                    unsigned char* __restrict__ wide, uint32_t* __restrict__ flags, uint32_t* __restrict__ items,
                    T* __restrict__ bounds,
                    const T* __restrict__ coords, const T* __restrict__ radii, const T* __restrict__ scene,
-                   uint32_t n) {
+                   uint32_t n, uint32_t first_window) {
     __shared__ T s_box[256][2][6];          // [split & 255][which child][lo xyz, hi xyz]
     __shared__ uint32_t s_grid[256][2][3];  // ... and its grid box
     __shared__ uint32_t s_far[256];         // arrival word of the in-window splits
     __shared__ uint32_t s_code[258];        // codes of positions first-1 .. last+1
     __shared__ uint32_t s_items;            // subtree roots handed on so far (HAND_OVER)
-    const uint32_t first = blockIdx.x * blockDim.x;
+    const uint32_t first = (first_window + blockIdx.x) * blockDim.x;   // (first_window: the sharded build runs a rank's own windows only)
     const uint32_t i = first + threadIdx.x;
     s_far[threadIdx.x] = NO_ARRIVAL;
     if (threadIdx.x == 0) s_items = 0;
@@ -500,6 +500,186 @@ leaf_bounds_kernel(T* __restrict__ bounds, const T* __restrict__ coords, const T
     store_box(bounds, node, leaf_box<T>(coords, radii, nodes[node].data[0]));
 }
 
+
+// ================================================================ sharded build (multi-GPU)
+// One process per GPU (collision_b200/sharded.py, mode "sharded_build").  The windows of the
+// sorted leaves are dealt out to the ranks; a rank runs the window pass for ITS windows only, the
+// roots it hands over are packed and all-gathered (a few per window), every rank finishes the few
+// nodes that span windows itself (top pass, replicated: it is small), and the in-window records
+// and leaf boxes of OTHER ranks' windows are fetched on demand -- only the subtrees that the
+// rank's own queries can enter -- straight from the owner's HBM over NVLink (peer loads; the
+// owners' buffers are mapped through CUDA IPC, ipc.cu).
+template <typename T> struct PackedItem {
+    uint32_t self, lo, hi, pad;   // node index (leaf: leaf_start + position), covered sorted positions [lo, hi]
+    T box[6];                     // exact box: lo xyz, hi xyz
+};
+constexpr uint32_t PACK_HEADER = 64;   // bytes: {count, overflow, ...} in front of a rank's packed items
+
+// own hand-over slots -> dense list (order arbitrary: the top pass does not depend on it)
+template <typename T>
+__global__ void __launch_bounds__(256)
+pack_items_kernel(const uint32_t* __restrict__ items, const col_node* __restrict__ nodes, const T* __restrict__ bounds,
+                  unsigned char* __restrict__ packed, uint32_t cap, uint32_t n, uint32_t leaf_begin, uint32_t leaf_end) {
+    const uint32_t s = leaf_begin + blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= leaf_end) return;
+    const uint32_t self = items[s];
+    if (self == NO_ARRIVAL) return;
+    uint32_t* hdr = reinterpret_cast<uint32_t*>(packed);
+    const uint32_t k = atomicAdd(hdr, 1u);
+    if (k >= cap) {
+        hdr[1] = 1u;   // overflow: reported by the host at its next synchronisation
+        return;
+    }
+    const uint32_t leaf_start = n - 1;
+    PackedItem<T> it;
+    it.self = self;
+    if (self >= leaf_start) {
+        it.lo = it.hi = self - leaf_start;
+    } else {
+        const uint2 rec = *reinterpret_cast<const uint2*>(nodes + self);   // {lo (window pass), right_edge}
+        it.lo = rec.x;
+        it.hi = rec.y;
+    }
+    it.pad = 0;
+    const T* b = bounds + (size_t)self * 8;
+    it.box[0] = b[0]; it.box[1] = b[1]; it.box[2] = b[2];
+    it.box[3] = b[4]; it.box[4] = b[5]; it.box[5] = b[6];
+    reinterpret_cast<PackedItem<T>*>(packed + PACK_HEADER)[k] = it;
+}
+
+// top pass over the gathered roots of ALL ranks (replicated on every rank)
+template <typename T>
+__global__ void __launch_bounds__(256)
+top_packed_kernel(const unsigned char* __restrict__ gathered, uint32_t cap, uint32_t world, uint32_t my_rank,
+                  const uint32_t* __restrict__ codes, col_node* __restrict__ nodes, unsigned char* __restrict__ wide,
+                  uint32_t* __restrict__ flags, T* __restrict__ bounds, const T* __restrict__ scene, uint32_t n) {
+    const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t r = (uint32_t)(t / cap), j = (uint32_t)(t % cap);
+    if (r >= world) return;
+    const size_t stride = PACK_HEADER + (size_t)cap * sizeof(PackedItem<T>);
+    const unsigned char* mine = gathered + r * stride;
+    if (j >= min(*reinterpret_cast<const uint32_t*>(mine), cap)) return;
+    const PackedItem<T> it = reinterpret_cast<const PackedItem<T>*>(mine + PACK_HEADER)[j];
+    Box<T> box;
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+        box.lo[k] = it.box[k];
+        box.hi[k] = it.box[3 + k];
+    }
+    // a sibling reads my box from the Bound array after my arrival: a remote root's box is not there yet
+    if (r != my_rank) store_box(bounds, it.self, box);
+    const Quant<T> qz = make_quant(scene);
+    const uint32_t leaf_start = n - 1, lo = it.lo, hi = it.hi;
+    const uint32_t code_lo = __ldg(codes + lo), code_hi = __ldg(codes + hi);
+    const int dl = lo > 0 ? key_delta(lo - 1, __ldg(codes + lo - 1), lo, code_lo) : -1;
+    const int dr = hi < leaf_start ? key_delta(hi, code_hi, hi + 1, __ldg(codes + hi + 1)) : -1;
+    top_climb(codes, nodes, wide, flags, bounds, qz, leaf_start, lo, hi, it.self, code_lo, code_hi, dl, dr, box,
+              quantise_box(qz, box.lo, box.hi));
+}
+
+// Which in-window subtrees of OTHER ranks can this rank's queries enter?  One thread per own root:
+// its box contains the boxes of all the queries below it, so a walk of the nodes that span windows
+// (all local after the top pass) with that box finds a superset of what those queries will visit.
+// A child whose leaves lie in one window is where the walk stops: if the window is another rank's
+// and nobody has asked for it yet, [first leaf, last leaf] goes on the fetch list.  Ranges follow
+// from Karras' numbering alone: the children of a node covering [lo, hi] with split g cover
+// [lo, g] and [g + 1, hi], g = the left child's index (internal) or position (leaf).
+template <typename T>
+__global__ void __launch_bounds__(256)
+halo_probe_kernel(const unsigned char* __restrict__ my_packed, uint32_t cap, const unsigned char* __restrict__ wide,
+                  const T* __restrict__ scene, uint32_t* __restrict__ asked, uint2* __restrict__ list,
+                  uint32_t* __restrict__ list_hdr, uint32_t list_cap, uint32_t n, uint32_t leaf_begin,
+                  uint32_t leaf_end) {
+    const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= min(*reinterpret_cast<const uint32_t*>(my_packed), cap)) return;
+    const PackedItem<T> it = reinterpret_cast<const PackedItem<T>*>(my_packed + PACK_HEADER)[j];
+    const Quant<T> qz = make_quant(scene);
+    T blo[3] = {it.box[0], it.box[1], it.box[2]}, bhi[3] = {it.box[3], it.box[4], it.box[5]};
+    const uint3 qg = quantise_query(qz, blo, bhi);
+    const uint32_t leaf_start = n - 1, my_lo = it.lo;
+    uint32_t st_idx[64], st_lo[64], st_hi[64];
+    int sp = 0;
+    uint32_t idx = 0, lo = 0, hi = leaf_start;
+    if ((lo >> 8) == (hi >> 8)) return;   // a single window: nothing spans windows
+    while (true) {
+        const uint4* rp = reinterpret_cast<const uint4*>(wide + (size_t)idx * QNODE_BYTES);
+        const uint4 r0 = rp[0], r1 = rp[1];
+        const bool la = (int32_t)r0.x < 0, lb = (int32_t)r0.y < 0;
+        const uint32_t g = r0.x & 0x7fffffffu;   // the split: left child's index = its last leaf (or the leaf itself)
+        // child a covers [lo, g], child b covers [g + 1, hi]; only leaves right of my first query matter
+        bool oa = grid_overlap(qg, r0.z, r0.w, r1.x) && g > my_lo;
+        bool ob = grid_overlap(qg, r1.y, r1.z, r1.w) && hi > my_lo;
+        const bool wa = (lo >> 8) == (g >> 8), wb = ((g + 1) >> 8) == (hi >> 8);   // child inside one window
+#pragma unroll
+        for (int c = 0; c < 2; c++) {
+            const bool o = c ? ob : oa, w = c ? wb : wa;
+            const uint32_t cl = c ? g + 1 : lo, ch = c ? hi : g;
+            if (o && w && (cl < leaf_begin || cl >= leaf_end)) {
+                if (atomicCAS(asked + cl, NO_ARRIVAL, NO_ARRIVAL - 1u) == NO_ARRIVAL) {
+                    const uint32_t k = atomicAdd(list_hdr, 1u);
+                    // (bit 31 of .y: the subtree is a LEFT child -- its root is node ch, else node cl; see halo_fetch_kernel)
+                    if (k < list_cap) list[k] = make_uint2(cl, ch | (c ? 0u : 0x80000000u));
+                    else list_hdr[1] = 1u;
+                }
+            }
+        }
+        (void)la; (void)lb;
+        const bool ta = oa && !wa, tb = ob && !wb;
+        if (ta && tb) {
+            st_idx[sp] = r0.y; st_lo[sp] = g + 1; st_hi[sp] = hi;
+            sp++;
+        }
+        if (ta) { idx = r0.x; hi = g; }
+        else if (tb) { idx = r0.y; lo = g + 1; }
+        else {
+            if (sp == 0) return;
+            sp--;
+            idx = st_idx[sp]; lo = st_lo[sp]; hi = st_hi[sp];
+        }
+    }
+}
+
+__device__ __forceinline__ uint4 ld_cg_u4(const uint4* p) {
+    uint4 v;
+    asm volatile("ld.global.cg.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+    return v;
+}
+
+// one warp per list entry: the subtree's records and its leaf boxes [cl, ch] from the owner's buffers into
+// mine.  Karras' numbering gives the ch - cl internal nodes of a subtree over [cl, ch] the indices cl..ch
+// without ONE end: a left child is numbered by its last leaf (the root is node ch, index cl belongs to a
+// node outside the subtree -- one that spans windows and is built locally), a right child by its first.
+__global__ void __launch_bounds__(256)
+halo_fetch_kernel(const uint2* __restrict__ list, const uint32_t* __restrict__ list_hdr, uint32_t list_cap,
+                  const unsigned long long* __restrict__ wide_table, const unsigned long long* __restrict__ bounds_table,
+                  const uint32_t* __restrict__ win_edges, uint32_t world, unsigned char* __restrict__ wide,
+                  unsigned char* __restrict__ bounds, uint32_t box_bytes, uint32_t n) {
+    const uint32_t count = min(list_hdr[0], list_cap);
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t leaf_start = n - 1;
+    for (uint32_t e = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); e < count; e += gridDim.x * (blockDim.x >> 5)) {
+        uint2 ent = list[e];
+        const bool left = (ent.y >> 31) != 0;
+        ent.y &= 0x7fffffffu;
+        const uint32_t w = ent.x >> 8;
+        uint32_t owner = 0;
+        while (owner + 1 < world && w >= win_edges[owner + 1]) owner++;
+        const unsigned char* src_w = reinterpret_cast<const unsigned char*>(wide_table[owner]);
+        const unsigned char* src_b = reinterpret_cast<const unsigned char*>(bounds_table[owner]);
+        // records: 32 bytes each = 2 x 16; leaf boxes: box_bytes each
+        const uint32_t nrec16 = (ent.y - ent.x) * 2, rec0 = ent.x + (left ? 1u : 0u);
+        for (uint32_t k = lane; k < nrec16; k += 32) {
+            const size_t off = (size_t)rec0 * QNODE_BYTES + (size_t)k * 16;
+            *reinterpret_cast<uint4*>(wide + off) = ld_cg_u4(reinterpret_cast<const uint4*>(src_w + off));
+        }
+        const uint32_t nbox16 = (ent.y - ent.x + 1) * (box_bytes / 16);
+        for (uint32_t k = lane; k < nbox16; k += 32) {
+            const size_t off = (size_t)(leaf_start + ent.x) * box_bytes + (size_t)k * 16;
+            *reinterpret_cast<uint4*>(bounds + off) = ld_cg_u4(reinterpret_cast<const uint4*>(src_b + off));
+        }
+    }
+}
+
 }  // namespace
 
 COL_API int col_refit(void* bounds, uint32_t* flags, const void* nodes, const void* coords4, const void* radii,
@@ -567,13 +747,13 @@ COL_API int col_build_refit_wide(const uint32_t* codes_sorted, const uint32_t* i
         if (two_pass) {                                                                                             \
             build_refit_kernel<T, true><<<blocks, BR_WINDOW, 0, s>>>(                                       \
                 codes_sorted, ids_sorted, (col_node*)nodes, (unsigned char*)wide, flags, items, (T*)bounds,         \
-                (const T*)coords4, (const T*)radii, (const T*)scene2x4, n);                                         \
+                (const T*)coords4, (const T*)radii, (const T*)scene2x4, n, 0u);                                     \
             build_refit_top_kernel<T><<<col_blocks(n, 256), 256, 0, s>>>(                                           \
                 codes_sorted, (col_node*)nodes, (unsigned char*)wide, flags, items, (T*)bounds, (const T*)scene2x4, n); \
         } else {                                                                                                    \
             build_refit_kernel<T, false><<<blocks, BR_WINDOW, 0, s>>>(                                      \
                 codes_sorted, ids_sorted, (col_node*)nodes, (unsigned char*)wide, flags, items, (T*)bounds,         \
-                (const T*)coords4, (const T*)radii, (const T*)scene2x4, n);                                         \
+                (const T*)coords4, (const T*)radii, (const T*)scene2x4, n, 0u);                                     \
         }                                                                                                           \
     } while (0)
     if (dtype == COL_F32) COL_BUILD_REFIT(float);
@@ -595,6 +775,99 @@ COL_API int col_leaf_bounds(void* bounds, const void* coords4, const void* radii
         leaf_bounds_kernel<double><<<blocks, 256, 0, col_stream(stream)>>>((double*)bounds, (const double*)coords4, (const double*)radii, (const col_node*)nodes, n);
     else
         return COL_ERR_UNSUPPORTED;
+    COL_CHECK_LAUNCH();
+    return 0;
+}
+
+// ---------------------------------------------------------------- sharded build: entry points
+COL_API size_t col_shard_packed_bytes(uint32_t cap, int dtype) {
+    return PACK_HEADER + (size_t)cap * (dtype == COL_F64 ? sizeof(PackedItem<double>) : sizeof(PackedItem<float>));
+}
+
+COL_API size_t col_shard_list_bytes(uint32_t list_cap) { return 16 + (size_t)list_cap * sizeof(uint2); }
+
+COL_API int col_shard_build_windows(const uint32_t* codes_sorted, const uint32_t* ids_sorted, void* nodes, void* wide,
+                                    uint32_t* flags, void* bounds, const void* coords4, const void* radii,
+                                    const void* scene2x4, int dtype, uint32_t n, uint32_t win_begin, uint32_t win_end,
+                                    void* packed, uint32_t cap, void* stream) {
+    if (!codes_sorted || !ids_sorted || !nodes || !wide || !flags || !bounds || !coords4 || !radii || !scene2x4 || !packed)
+        return COL_ERR_BAD_ARG;
+    if (dtype != COL_F32 && dtype != COL_F64) return COL_ERR_UNSUPPORTED;
+    const uint32_t windows = col_blocks(n, BR_WINDOW);
+    if (n < 2 || win_begin > win_end || win_end > windows || cap == 0) return COL_ERR_BAD_ARG;
+    cudaStream_t s = col_stream(stream);
+    // flags: [0, n-1) arrival words of the cross-window splits, [n, 2n) hand-over slots / fetch marks
+    COL_CUDA(cudaMemsetAsync(flags, 0xFF, sizeof(uint32_t) * 2 * (size_t)n, s));
+    COL_CUDA(cudaMemsetAsync(packed, 0, PACK_HEADER, s));
+    if (win_begin == win_end) return 0;
+    uint32_t* items = flags + n;
+    const uint32_t leaf_begin = win_begin * BR_WINDOW, leaf_end = min(win_end * BR_WINDOW, n);
+    const unsigned blocks = win_end - win_begin, pblocks = col_blocks(leaf_end - leaf_begin, 256);
+    if (dtype == COL_F32) {
+        build_refit_kernel<float, true><<<blocks, BR_WINDOW, 0, s>>>(
+            codes_sorted, ids_sorted, (col_node*)nodes, (unsigned char*)wide, flags, items, (float*)bounds,
+            (const float*)coords4, (const float*)radii, (const float*)scene2x4, n, win_begin);
+        pack_items_kernel<float><<<pblocks, 256, 0, s>>>(items, (const col_node*)nodes, (const float*)bounds,
+                                                         (unsigned char*)packed, cap, n, leaf_begin, leaf_end);
+    } else {
+        build_refit_kernel<double, true><<<blocks, BR_WINDOW, 0, s>>>(
+            codes_sorted, ids_sorted, (col_node*)nodes, (unsigned char*)wide, flags, items, (double*)bounds,
+            (const double*)coords4, (const double*)radii, (const double*)scene2x4, n, win_begin);
+        pack_items_kernel<double><<<pblocks, 256, 0, s>>>(items, (const col_node*)nodes, (const double*)bounds,
+                                                          (unsigned char*)packed, cap, n, leaf_begin, leaf_end);
+    }
+    COL_CHECK_LAUNCH();
+    return 0;
+}
+
+COL_API int col_shard_top(const void* gathered, uint32_t cap, uint32_t world, uint32_t my_rank,
+                          const uint32_t* codes_sorted, void* nodes, void* wide, uint32_t* flags, void* bounds,
+                          const void* scene2x4, int dtype, uint32_t n, void* stream) {
+    if (!gathered || !codes_sorted || !nodes || !wide || !flags || !bounds || !scene2x4 || cap == 0 || world == 0 ||
+        my_rank >= world)
+        return COL_ERR_BAD_ARG;
+    if (dtype != COL_F32 && dtype != COL_F64) return COL_ERR_UNSUPPORTED;
+    cudaStream_t s = col_stream(stream);
+    const unsigned blocks = col_blocks((uint64_t)cap * world, 256);
+    if (dtype == COL_F32)
+        top_packed_kernel<float><<<blocks, 256, 0, s>>>((const unsigned char*)gathered, cap, world, my_rank, codes_sorted,
+                                                        (col_node*)nodes, (unsigned char*)wide, flags, (float*)bounds,
+                                                        (const float*)scene2x4, n);
+    else
+        top_packed_kernel<double><<<blocks, 256, 0, s>>>((const unsigned char*)gathered, cap, world, my_rank, codes_sorted,
+                                                         (col_node*)nodes, (unsigned char*)wide, flags, (double*)bounds,
+                                                         (const double*)scene2x4, n);
+    COL_CHECK_LAUNCH();
+    return 0;
+}
+
+COL_API int col_shard_halo(const void* gathered, uint32_t cap, uint32_t world, uint32_t my_rank, void* wide, void* bounds,
+                           const void* scene2x4, int dtype, uint32_t* flags, void* list, uint32_t list_cap,
+                           const uint64_t* wide_table, const uint64_t* bounds_table, const uint32_t* win_edges,
+                           uint32_t n, uint32_t leaf_begin, uint32_t leaf_end, void* stream) {
+    if (!gathered || !wide || !bounds || !scene2x4 || !flags || !list || !wide_table || !bounds_table || !win_edges ||
+        cap == 0 || list_cap == 0 || my_rank >= world)
+        return COL_ERR_BAD_ARG;
+    if (dtype != COL_F32 && dtype != COL_F64) return COL_ERR_UNSUPPORTED;
+    cudaStream_t s = col_stream(stream);
+    COL_CUDA(cudaMemsetAsync(list, 0, 16, s));
+    uint32_t* hdr = reinterpret_cast<uint32_t*>(list);
+    uint2* entries = reinterpret_cast<uint2*>(reinterpret_cast<unsigned char*>(list) + 16);
+    const size_t stride = col_shard_packed_bytes(cap, dtype);
+    const unsigned char* mine = reinterpret_cast<const unsigned char*>(gathered) + my_rank * stride;
+    uint32_t* asked = flags + n;
+    const unsigned pblocks = col_blocks(cap, 256);
+    if (dtype == COL_F32)
+        halo_probe_kernel<float><<<pblocks, 256, 0, s>>>(mine, cap, (const unsigned char*)wide, (const float*)scene2x4, asked,
+                                                         entries, hdr, list_cap, n, leaf_begin, leaf_end);
+    else
+        halo_probe_kernel<double><<<pblocks, 256, 0, s>>>(mine, cap, (const unsigned char*)wide, (const double*)scene2x4,
+                                                          asked, entries, hdr, list_cap, n, leaf_begin, leaf_end);
+    COL_CHECK_LAUNCH();
+    halo_fetch_kernel<<<COL_NUM_SMS * 8, 256, 0, s>>>(entries, hdr, list_cap, (const unsigned long long*)wide_table,
+                                                      (const unsigned long long*)bounds_table, win_edges, world,
+                                                      (unsigned char*)wide, (unsigned char*)bounds,
+                                                      dtype == COL_F64 ? 64u : 32u, n);
     COL_CHECK_LAUNCH();
     return 0;
 }

@@ -177,7 +177,8 @@ class ShardedCollider:
     reference's counter) on every rank, `collisions_buf` = this rank's rows
     (`local_pairs` of them, global row index `pair_base` + i)."""
 
-    MODES = ("broadcast_tree", "replicate_build", "gather_inputs")
+    MODES = ("broadcast_tree", "replicate_build", "gather_inputs", "sharded_build")
+    WINDOW = 256      # sorted leaves per window of the build (csrc/refit.cu: BR_WINDOW)
 
     def __init__(self, ctx, size, ngroups, group_size, coord_dtype=dtype('float32'), group=None, src=0,
                  mode="broadcast_tree", balance=False, query_weight=1, graph=False):
@@ -190,6 +191,14 @@ class ShardedCollider:
         mode "gather_inputs": as "replicate_build", but the scene arrives sharded -- every rank
         owns the spheres [size*r/k, size*(r+1)/k) -- and is all-gathered in place (the same
         bytes over NVLink, but k host links feed it instead of one).
+        mode "sharded_build": the scene arrives sharded as in "gather_inputs" and the sort is replicated, but
+        the BUILD is dealt out: the 256-leaf windows of the sorted order are split between the ranks, a rank
+        builds and refits its own windows only, the few subtree roots per window that reach beyond it are
+        all-gathered and every rank finishes the nodes that span windows itself; the records and leaf boxes
+        of other ranks' windows are then fetched ON DEMAND -- only the subtrees the rank's own queries can
+        enter -- straight from the owners' HBM over NVLink (peer loads from buffers mapped with CUDA IPC,
+        `collision_b200.shared`).  Query ranges = the window ranges (no `balance`).  Constructing the object
+        is collective (the shared buffers are exchanged).
         balance=True: after every call (with sync_totals) that WRITES rows the query ranges of
         the next call are re-cut from the all-gathered row totals (cost of a range = rows +
         query_weight * queries, accumulated in a `DensityModel`), so that a clustered scene
@@ -224,6 +233,43 @@ class ShardedCollider:
         self._graphs = {}
         self._graph_candidate = None
         self.graph_replays = 0
+        if mode == "sharded_build":
+            if balance:
+                raise ValueError("mode 'sharded_build' splits the queries where it splits the windows: no balance")
+            self._setup_sharded_build(ctx)
+
+    def _setup_sharded_build(self, ctx):
+        from .shared import SharedBuffer
+        c, n, k = self.collider, self.size, self.world
+        L = _lib.lib()
+        windows = -(-n // self.WINDOW)
+        self.win_edges = [windows * r // k for r in range(k + 1)]
+        self.edges = [min(w * self.WINDOW, n) for w in self.win_edges]
+        self.q_begin, self.q_end = self.edges[self.rank], self.edges[self.rank + 1]
+        c._ensure_scratch(None)
+        isz = c.program.coord_dtype.itemsize
+        # the two arrays the walk reads live in buffers every rank of the box can read in place
+        self._sb_wide = SharedBuffer(ctx, c._wide_buf.numel(), self.group)
+        self._sb_bounds = SharedBuffer(ctx, c._bounds_buf.numel(), self.group)
+        c._wide_buf, c._bounds_buf = self._sb_wide.local, self._sb_bounds.local
+        most = max(e - b for b, e in zip(self.edges, self.edges[1:]))
+        self._cap = max(1024, most // 16)                    # subtree roots a rank may hand over (typically 1.6 % of its leaves)
+        self._list_cap = max(4096, n // 16)                  # remote subtrees a rank may ask for
+        nb = L.col_shard_packed_bytes(self._cap, c.program._code)
+        self._packed = _lib.alloc_bytes(ctx, nb)
+        self._gathered = _lib.alloc_bytes(ctx, nb * k)
+        self._list = _lib.alloc_bytes(ctx, L.col_shard_list_bytes(self._list_cap))
+        self._win_edges_dev = torch.tensor(self.win_edges, dtype=torch.int32, device=ctx)
+        dist.barrier(group=self.group)
+
+    def _check_shard_overflow(self):
+        hdr = self._gathered.view(torch.int32)
+        stride = self._packed.numel() // 4
+        over = any(int(hdr[r * stride + 1].item()) for r in range(self.world)) or \
+            int(self._list.view(torch.int32)[1].item())
+        if over:
+            raise RuntimeError("sharded_build: more subtree roots / remote subtrees than the exchange buffers hold "
+                               "(cap {}, list {}); use mode 'gather_inputs' for this scene".format(self._cap, self._list_cap))
 
     def suggested_capacity(self, headroom=1.5):
         """Rows to make room for on this rank after a count-only call: with balance=True the
@@ -301,11 +347,36 @@ class ShardedCollider:
             self.local_pairs = t[self.rank]
             self.pair_base = sum(t[:self.rank])
             self.total_pairs = sum(t)
+            if self.mode == "sharded_build":
+                self._check_shard_overflow()
             if n_collisions > 0:
                 self.overflowed = self.local_pairs > n_collisions
                 if self.balance:     # (count-only calls never move the cuts: see __init__)
                     self._recut(t)
         return ev
+
+    def _build_sharded(self, cq, coords_buf, radii_buf):
+        """Own windows -> all-gather of the handed-over roots -> spanning nodes (replicated) -> halo fetch."""
+        c = self.collider
+        L, P, S = _lib.lib(), _lib.ptr, _lib.stream_ptr(cq)
+        n, code = self.size, c.program._code
+        _lib.check(L.col_shard_build_windows(P(c._codes_bufs[1]), P(c._ids_bufs[1]), P(c._nodes_buf), P(c._wide_buf),
+                                             P(c._flags_buf), P(c._bounds_buf), P(coords_buf), P(radii_buf),
+                                             P(c._scene_buf), code, n, self.win_edges[self.rank],
+                                             self.win_edges[self.rank + 1], P(self._packed), self._cap, S),
+                   "col_shard_build_windows")
+        c._mark(cq, "build_windows", 2)
+        dist.all_gather_into_tensor(self._gathered, self._packed, group=self.group)
+        c._mark(cq, "gather_roots", 0)
+        _lib.check(L.col_shard_top(P(self._gathered), self._cap, self.world, self.rank, P(c._codes_bufs[1]),
+                                   P(c._nodes_buf), P(c._wide_buf), P(c._flags_buf), P(c._bounds_buf),
+                                   P(c._scene_buf), code, n, S), "col_shard_top")
+        c._mark(cq, "build_top", 1)
+        _lib.check(L.col_shard_halo(P(self._gathered), self._cap, self.world, self.rank, P(c._wide_buf),
+                                    P(c._bounds_buf), P(c._scene_buf), code, P(c._flags_buf), P(self._list),
+                                    self._list_cap, P(self._sb_wide.table), P(self._sb_bounds.table),
+                                    P(self._win_edges_dev), n, self.q_begin, self.q_end, S), "col_shard_halo")
+        c._mark(cq, "halo", 2)
 
     def _enqueue(self, cq, coords_buf, radii_buf, n_collisions_buf, collisions_buf, n_collisions):
         c = self.collider
@@ -318,7 +389,7 @@ class ShardedCollider:
                 broadcast_buffers(self._shared_buffers(), self.src, self.group)
                 c._mark(cq, "broadcast", 0)
             else:
-                if self.mode == "gather_inputs":
+                if self.mode in ("gather_inputs", "sharded_build"):
                     isz = c.program.coord_dtype.itemsize
                     gather_slices(coords_buf, 4 * isz, self.size, self.group)
                     gather_slices(radii_buf, isz, self.size, self.group)
@@ -326,7 +397,10 @@ class ShardedCollider:
                     broadcast_buffers([coords_buf, radii_buf], self.src, self.group)
                 c._mark(cq, "broadcast", 0)
                 c._sort_stage(cq, coords_buf)
-                c._build_wide(cq, coords_buf, radii_buf)
+                if self.mode == "sharded_build":
+                    self._build_sharded(cq, coords_buf, radii_buf)
+                else:
+                    c._build_wide(cq, coords_buf, radii_buf)
             c._walk_range(cq, collisions_buf, n_collisions, self.q_begin, self.q_end)
             self._totals = exchange_totals(c._total_buf, self.group)
             total = self._totals.sum().reshape(1)

@@ -283,6 +283,47 @@ int col_compat_reduce1(const void* values, uint64_t n, int dtype, uint32_t lanes
 int col_compat_reduce2(void* group_accs, void* output, int dtype, uint32_t lanes, const int* h_ops, uint32_t n_acc,
                        uint32_t ngroups, void* stream);
 
+/* ------------------------------------------------ buffers shared across ranks (ipc.cu)
+ * Multi-GPU only (no reference counterpart: upstream is single-device).  One process per GPU;
+ * a rank exports a cudaMalloc allocation as a 64-byte CUDA IPC handle (host memory), the
+ * other ranks of the same box open it on their own device and read it from their kernels
+ * over NVLink.  These are the only entry points that allocate. */
+int col_ipc_alloc(void** ptr, uint64_t bytes);
+int col_ipc_free(void* ptr);
+int col_ipc_export(void* ptr, void* h_handle64);
+int col_ipc_open(void** ptr, const void* h_handle64);
+int col_ipc_close(void* ptr);
+
+/* ------------------------------------------------ sharded build (multi-GPU, refit.cu)
+ * No reference counterpart.  The windows (256 sorted leaves each) are dealt out to the ranks:
+ * col_shard_build_windows  = col_build_refit_wide's window pass for windows [win_begin, win_end) only; the
+ *                            subtree roots it hands over are packed into `packed` ({count, overflow} header +
+ *                            up to `cap` records {node, lo, hi, box}; col_shard_packed_bytes(cap, dtype) bytes).
+ *                            The caller all-gathers the ranks' packed buffers (rank-major) into `gathered`.
+ * col_shard_top            = the pass over the nodes that span windows, from the gathered roots of ALL ranks
+ *                            (replicated on every rank: it is small).
+ * col_shard_halo           = which in-window subtrees of OTHER ranks can this rank's queries enter (a walk of
+ *                            the spanning nodes with each own root's box), and their records + leaf boxes
+ *                            copied from the owners' buffers (wide_table / bounds_table: the ranks' base
+ *                            addresses as mapped into this process, col_ipc_open) into `wide` / `bounds`.
+ *                            win_edges: world + 1 window indices (device), rank r owns [win_edges[r], win_edges[r+1]);
+ *                            list: col_shard_list_bytes(list_cap) bytes of scratch.  After it the traversal of
+ *                            the rank's own queries [leaf_begin, leaf_end) finds everything it touches locally.
+ * Overflow of `cap` / `list_cap` sets word 1 of the respective header (the host checks it when it next syncs). */
+size_t col_shard_packed_bytes(uint32_t cap, int dtype);
+size_t col_shard_list_bytes(uint32_t list_cap);
+int col_shard_build_windows(const uint32_t* codes_sorted, const uint32_t* ids_sorted, void* nodes, void* wide,
+                            uint32_t* flags, void* bounds, const void* coords4, const void* radii,
+                            const void* scene2x4, int dtype, uint32_t n, uint32_t win_begin, uint32_t win_end,
+                            void* packed, uint32_t cap, void* stream);
+int col_shard_top(const void* gathered, uint32_t cap, uint32_t world, uint32_t my_rank,
+                  const uint32_t* codes_sorted, void* nodes, void* wide, uint32_t* flags, void* bounds,
+                  const void* scene2x4, int dtype, uint32_t n, void* stream);
+int col_shard_halo(const void* gathered, uint32_t cap, uint32_t world, uint32_t my_rank, void* wide, void* bounds,
+                   const void* scene2x4, int dtype, uint32_t* flags, void* list, uint32_t list_cap,
+                   const uint64_t* wide_table, const uint64_t* bounds_table, const uint32_t* win_edges,
+                   uint32_t n, uint32_t leaf_begin, uint32_t leaf_end, void* stream);
+
 /* utility: u32 fill (cl.enqueue_fill_buffer sites, e.g. collision/offset.py:43) */
 int col_fill_u32(uint32_t* dst, uint32_t value, uint64_t n, void* stream);
 /* range (collision/collision.cl:8-10): ids[i] = i for i < n */

@@ -1,0 +1,62 @@
+"""Development aid (torchrun, 2+ GPUs): one ShardedCollider(mode=...) call on a small scene, rows checked
+against the single-GPU Collider on every rank.  python -m torch.distributed.run ... tools/shard_debug.py [--spheres N] [--mode M]"""
+import argparse
+import datetime
+import os
+import sys
+from pathlib import Path
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+ROOT = Path(__file__).resolve().parent.parent
+sys.path.insert(0, str(ROOT))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--spheres", type=int, default=20011)
+    ap.add_argument("--mode", default="sharded_build")
+    ap.add_argument("--steps", type=int, default=3)
+    args = ap.parse_args()
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    dev = torch.device("cuda", int(os.environ.get("LOCAL_RANK", "0")))
+    torch.cuda.set_device(dev)
+    dist.init_process_group("nccl", device_id=dev, timeout=datetime.timedelta(seconds=60))
+    from collision_b200.collision import Collider
+    from collision_b200.sharded import ShardedCollider
+    n = args.spheres
+    g = torch.Generator(device=dev).manual_seed(5)
+    coords = torch.zeros(n, 4, device=dev)
+    coords[:, :3] = torch.rand(n, 3, device=dev, generator=g)
+    radii = torch.full((n,), 0.5 * n ** (-1.0 / 3.0), device=dev)
+    cq = torch.cuda.Stream(dev)
+    one = Collider(dev, n, 8, 128)
+    nb = torch.zeros(1, dtype=torch.int32, device=dev)
+    torch.cuda.synchronize()
+    one.get_collisions(cq, coords, radii, nb, None, 0).synchronize()
+    total = int(nb.item()) & 0xFFFFFFFF
+    want = torch.empty(max(total, 1) * 2, dtype=torch.int32, device=dev)
+    one.get_collisions(cq, coords, radii, nb, want, total).synchronize()
+    print("rank {} single-GPU total {}".format(rank, total), flush=True)
+    col = ShardedCollider(dev, n, 8, 128, mode=args.mode)
+    print("rank {} sharded collider up: queries [{}, {})".format(rank, col.q_begin, col.q_end), flush=True)
+    col.get_collisions(cq, coords.clone(), radii.clone(), nb, None, 0).synchronize()
+    print("rank {} count-only: local {} base {} total {}".format(rank, col.local_pairs, col.pair_base, col.total_pairs), flush=True)
+    cap = col.local_pairs
+    rows = torch.empty(max(cap, 1) * 2, dtype=torch.int32, device=dev)
+    for step in range(args.steps):
+        col.get_collisions(cq, coords.clone(), radii.clone(), nb, rows, cap).synchronize()
+        ok = col.total_pairs == total and bool((rows[:cap * 2] == want[col.pair_base * 2:(col.pair_base + cap) * 2]).all())
+        print("rank {} step {} rows equal: {}".format(rank, step, ok), flush=True)
+    if args.mode == "sharded_build":
+        lst = col._list.view(torch.int32)
+        print("rank {} roots packed {} of cap {}, remote subtrees fetched {} of {}".format(
+            rank, int(col._packed.view(torch.int32)[0].item()), col._cap, int(lst[0].item()), col._list_cap), flush=True)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
