@@ -792,6 +792,7 @@ def run_multi(args):
             dist.broadcast(flag, src=0)
             res["parity"] = bool(flag[0].item())
             res["n1_ms"] = n1
+        col.close()
         del col, pairs_d, coords_d, radii_d, full_c, full_r
         torch.cuda.empty_cache()
         return res
@@ -891,7 +892,10 @@ def main():
     ap.add_argument("--time-n1", action="store_true", default=True,
                     help="N>1: also time the single-GPU Collider on the same scene (rank 0, outside the timed region)")
     ap.add_argument("--multi-gpu-mode", choices=["broadcast_tree", "replicate_build", "gather_inputs", "sharded_build"],
-                    default="gather_inputs")
+                    default="sharded_build",
+                    help="N>1: sharded_build (default: build dealt out, other ranks' subtrees fetched on demand over "
+                         "NVLink), gather_inputs / replicate_build (build replicated), broadcast_tree (north_star's "
+                         "literal form: rank 0 builds, the tree is broadcast)")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

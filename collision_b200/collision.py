@@ -260,6 +260,12 @@ class Collider:
         _lib.check(L.col_morton(P(self._codes_bufs[0]), P(self._ids_bufs[0]), P(coords_buf), P(scene),
                                 code, n, n, S), "col_morton")
         mark(cq, "morton", 1)
+        self._sort_codes(cq)
+
+    def _sort_codes(self, cq):
+        """Stable sort of (_codes_bufs[0], _ids_bufs[0]) into (_codes_bufs[1], _ids_bufs[1])."""
+        L, P, S = _lib.lib(), _lib.ptr, _lib.stream_ptr(cq)
+        n, mark = self.size, self._mark
         # padding keys are not needed by this sort: only the n real keys move
         _lib.check(L.col_sort_pairs(P(self._codes_bufs[0]), P(self._codes_bufs[1]), P(self._ids_bufs[0]),
                                     P(self._ids_bufs[1]), n, 4, 4, MORTON_BITS, P(self.sorter._ensure_scratch(cq=cq)), S),

@@ -260,6 +260,7 @@ class ShardedCollider:
         self._gathered = _lib.alloc_bytes(ctx, nb * k)
         self._list = _lib.alloc_bytes(ctx, L.col_shard_list_bytes(self._list_cap))
         self._win_edges_dev = torch.tensor(self.win_edges, dtype=torch.int32, device=ctx)
+        self._side = torch.cuda.Stream(_lib.device_of(ctx))
         dist.barrier(group=self.group)
 
     def _check_shard_overflow(self):
@@ -270,6 +271,20 @@ class ShardedCollider:
         if over:
             raise RuntimeError("sharded_build: more subtree roots / remote subtrees than the exchange buffers hold "
                                "(cap {}, list {}); use mode 'gather_inputs' for this scene".format(self._cap, self._list_cap))
+
+    def close(self):
+        """Collective teardown: drops the captured graphs (they hold NCCL work) and unmaps / frees the
+        buffers shared between the ranks.  Call it on every rank before destroy_process_group()."""
+        self._graphs.clear()
+        self._graph_candidate = None
+        torch.cuda.synchronize()
+        if self.mode == "sharded_build" and getattr(self, "_sb_wide", None) is not None:
+            c = self.collider
+            c._wide_buf = c._bounds_buf = None
+            c._bufs_for = None
+            self._sb_wide.close()
+            self._sb_bounds.close()
+            self._sb_wide = self._sb_bounds = None
 
     def suggested_capacity(self, headroom=1.5):
         """Rows to make room for on this rank after a count-only call: with balance=True the
@@ -355,6 +370,48 @@ class ShardedCollider:
                     self._recut(t)
         return ev
 
+    def _front_sharded(self, cq, coords_buf, radii_buf):
+        """Scene bounds and Morton codes from the rank's OWN slice of the spheres (a 32-byte all-reduce and
+        an all-gather of 4 bytes per sphere), then the replicated sort -- while the all-gather of the
+        coordinates and radii themselves (20 bytes per sphere, needed only by the leaf boxes of the build)
+        runs beside it on a second stream."""
+        c = self.collider
+        L, P, S = _lib.lib(), _lib.ptr, _lib.stream_ptr(cq)
+        n, code, isz = self.size, c.program._code, c.program.coord_dtype.itemsize
+        b, e = shard_range(n, self.world, self.rank)
+        fdt = torch.float32 if isz == 4 else torch.float64
+        scene = c._scene_buf.view(fdt)                       # {min[4], max[4]}
+        if e > b:
+            _lib.check(L.col_bounds(P(coords_buf) + b * 4 * isz, e - b, code, 4, P(c._scene_buf),
+                                    P(c.reducer._ensure_scratch(cq)), S), "col_bounds")
+        else:
+            scene[:4] = float("inf")
+            scene[4:] = float("-inf")
+        # one MIN all-reduce of {min, -max}: exact (negation and min are), so every rank holds the bounds a
+        # single device would have computed
+        scene[4:].neg_()
+        dist.all_reduce(scene, op=dist.ReduceOp.MIN, group=self.group)
+        scene[4:].neg_()
+        c._mark(cq, "bounds", 1)
+        if e > b:
+            _lib.check(L.col_morton(P(c._codes_bufs[0]) + 4 * b, None, P(coords_buf) + b * 4 * isz, P(c._scene_buf),
+                                    code, e - b, e - b, S), "col_morton")
+        gather_slices(c._codes_bufs[0][:4 * n], 4, n, self.group)
+        _lib.check(L.col_range(P(c._ids_bufs[0]), n, S), "col_range")
+        c._mark(cq, "morton", 2)
+        # the scene itself travels on the side stream, behind the codes in NCCL's order
+        ready = torch.cuda.Event()
+        ready.record(cq)
+        with torch.cuda.stream(self._side):
+            self._side.wait_event(ready)
+            gather_slices(coords_buf, 4 * isz, n, self.group)
+            gather_slices(radii_buf, isz, n, self.group)
+            gathered = torch.cuda.Event()
+            gathered.record(self._side)
+        c._sort_codes(cq)
+        cq.wait_event(gathered)
+        c._mark(cq, "broadcast", 0)      # (what is left of the scene's all-gather after the sort)
+
     def _build_sharded(self, cq, coords_buf, radii_buf):
         """Own windows -> all-gather of the handed-over roots -> spanning nodes (replicated) -> halo fetch."""
         c = self.collider
@@ -388,8 +445,11 @@ class ShardedCollider:
                     c._build_wide(cq, coords_buf, radii_buf)
                 broadcast_buffers(self._shared_buffers(), self.src, self.group)
                 c._mark(cq, "broadcast", 0)
+            elif self.mode == "sharded_build":
+                self._front_sharded(cq, coords_buf, radii_buf)
+                self._build_sharded(cq, coords_buf, radii_buf)
             else:
-                if self.mode in ("gather_inputs", "sharded_build"):
+                if self.mode == "gather_inputs":
                     isz = c.program.coord_dtype.itemsize
                     gather_slices(coords_buf, 4 * isz, self.size, self.group)
                     gather_slices(radii_buf, isz, self.size, self.group)
@@ -397,10 +457,7 @@ class ShardedCollider:
                     broadcast_buffers([coords_buf, radii_buf], self.src, self.group)
                 c._mark(cq, "broadcast", 0)
                 c._sort_stage(cq, coords_buf)
-                if self.mode == "sharded_build":
-                    self._build_sharded(cq, coords_buf, radii_buf)
-                else:
-                    c._build_wide(cq, coords_buf, radii_buf)
+                c._build_wide(cq, coords_buf, radii_buf)
             c._walk_range(cq, collisions_buf, n_collisions, self.q_begin, self.q_end)
             self._totals = exchange_totals(c._total_buf, self.group)
             total = self._totals.sum().reshape(1)

@@ -93,6 +93,7 @@ def _worker(rank, world, port, n, kind, mode, balance, graph, frames, raw, tmpdi
         if graph:
             assert col.graph_replays >= frames - 2, col.graph_replays
         np.save(os.path.join(tmpdir, "log{}.npy".format(rank)), np.array(log))
+        col.close()
     finally:
         dist.destroy_process_group()
 

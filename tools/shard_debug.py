@@ -19,7 +19,10 @@ def main():
     ap.add_argument("--spheres", type=int, default=20011)
     ap.add_argument("--mode", default="sharded_build")
     ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--graph", action="store_true", help="sync_totals=False calls: plain, plain, capture, replay ...")
     args = ap.parse_args()
+    import faulthandler
+    faulthandler.dump_traceback_later(90, exit=True)      # a hang shows where
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
     dev = torch.device("cuda", int(os.environ.get("LOCAL_RANK", "0")))
     torch.cuda.set_device(dev)
@@ -40,22 +43,33 @@ def main():
     want = torch.empty(max(total, 1) * 2, dtype=torch.int32, device=dev)
     one.get_collisions(cq, coords, radii, nb, want, total).synchronize()
     print("rank {} single-GPU total {}".format(rank, total), flush=True)
-    col = ShardedCollider(dev, n, 8, 128, mode=args.mode)
+    col = ShardedCollider(dev, n, 8, 128, mode=args.mode, graph=args.graph)
     print("rank {} sharded collider up: queries [{}, {})".format(rank, col.q_begin, col.q_end), flush=True)
     col.get_collisions(cq, coords.clone(), radii.clone(), nb, None, 0).synchronize()
     print("rank {} count-only: local {} base {} total {}".format(rank, col.local_pairs, col.pair_base, col.total_pairs), flush=True)
     cap = col.local_pairs
     rows = torch.empty(max(cap, 1) * 2, dtype=torch.int32, device=dev)
+    cc, rr = coords.clone(), radii.clone()
     for step in range(args.steps):
-        col.get_collisions(cq, coords.clone(), radii.clone(), nb, rows, cap).synchronize()
+        if args.graph:
+            cc.copy_(coords); rr.copy_(radii); torch.cuda.synchronize()
+            print("rank {} step {} enqueue (graphs {}, replays {})".format(rank, step, len(col._graphs), col.graph_replays), flush=True)
+            col.get_collisions(cq, cc, rr, nb, rows, cap, sync_totals=False).synchronize()
+            t = col._totals.tolist()
+            col.total_pairs, col.pair_base = sum(t), sum(t[:rank])
+        else:
+            col.get_collisions(cq, coords.clone(), radii.clone(), nb, rows, cap).synchronize()
         ok = col.total_pairs == total and bool((rows[:cap * 2] == want[col.pair_base * 2:(col.pair_base + cap) * 2]).all())
         print("rank {} step {} rows equal: {}".format(rank, step, ok), flush=True)
     if args.mode == "sharded_build":
         lst = col._list.view(torch.int32)
         print("rank {} roots packed {} of cap {}, remote subtrees fetched {} of {}".format(
             rank, int(col._packed.view(torch.int32)[0].item()), col._cap, int(lst[0].item()), col._list_cap), flush=True)
+    col.close()
+    print("rank {} closed".format(rank), flush=True)
     dist.barrier()
     dist.destroy_process_group()
+    print("rank {} process group destroyed".format(rank), flush=True)
 
 
 if __name__ == "__main__":
