@@ -30,6 +30,7 @@ SIGNATURES = {
     "col_morton": (_int, [_vp, _vp, _vp, _vp, _int, _u32, _u32, _vp]),
     "col_scan_scratch_bytes": (_sz, [_u64]),
     "col_exclusive_scan_u32": (_int, [_vp, _u64, _vp, _vp, _vp]),
+    "col_exclusive_scan_u32_static": (_int, [_vp, _u64, _vp, _vp]),
     "col_sort_scratch_bytes": (_sz, [_u64, _u32, _u32]),
     "col_sort_pairs": (_int, [_vp, _vp, _vp, _vp, _u64, _u32, _u32, _u32, _vp, _vp]),
     "col_radix_pass": (_int, [_vp, _vp, _vp, _vp, _u64, _u32, _u32, _u32, _u32, _vp, _vp]),

@@ -11,6 +11,9 @@
 // tile can only wait on tiles that already started (forward progress).
 // Results wrap mod 2^32 exactly like the reference's uint arithmetic; the u64
 // grand total (62-bit) is produced for the pair compaction.
+#include <cstdio>
+#include <mutex>
+
 #include "common.cuh"
 
 namespace {
@@ -332,6 +335,68 @@ COL_API int col_exclusive_scan_u32(uint32_t* data, uint64_t n, uint64_t* total_o
             return 0;
         }
     }
+    COL_CUDA(cudaMemsetAsync(scratch, 0, SCAN_STATUS_OFF + (size_t)tiles * sizeof(uint64_t), s));
+    unsigned* ticket = reinterpret_cast<unsigned*>(scratch);
+    uint64_t* status = reinterpret_cast<uint64_t*>(reinterpret_cast<char*>(scratch) + SCAN_STATUS_OFF);
+    scan_kernel<<<(unsigned)tiles, SCAN_THREADS, 0, s>>>(data, n, total_out, ticket, status);
+    COL_CHECK_LAUNCH();
+    return 0;
+}
+
+// ---------------------------------------------------------------- no-allocation variant
+// col_exclusive_scan_u32_static: the single-pass look-back scan above with its ticket and status
+// words in a file-scope device array instead of caller scratch, for callers that cannot allocate
+// (CUDA graph capture, serving loops).  No counterpart in the reference.
+// Every GPU that loads the library holds the array until exit; every call on
+// a device shares it, so calls that overlap on that GPU (two streams, two threads) race.
+// The array keeps the previous call's flags: the part this call uses is cleared first, in stream order.
+namespace {
+
+constexpr uint64_t SCAN_STATIC_TILES = (COL_SCAN_STATIC_MAX_N + SCAN_TILE - 1) / SCAN_TILE;
+constexpr size_t SCAN_STATIC_BYTES = SCAN_STATUS_OFF + SCAN_STATIC_TILES * sizeof(uint64_t);   // 16,640 B
+
+static __device__ __align__(256) unsigned char g_scan_static[SCAN_STATIC_BYTES];
+
+constexpr int SCAN_STATIC_MAX_DEVICES = 64;
+std::mutex g_scan_static_mutex;
+void* g_scan_static_ptr[SCAN_STATIC_MAX_DEVICES];   // device address of g_scan_static, per device
+
+// In host code `g_scan_static` is only a handle for the runtime, not a device address: resolve it
+// once per device, with that device current.
+int scan_static_address(void** out) {
+    int dev = -1;
+    COL_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= SCAN_STATIC_MAX_DEVICES) return COL_ERR_UNSUPPORTED;
+    std::lock_guard<std::mutex> lock(g_scan_static_mutex);
+    if (!g_scan_static_ptr[dev]) {
+        void* p = nullptr;
+        COL_CUDA(cudaGetSymbolAddress(&p, g_scan_static));
+        if (!p) return (int)cudaErrorInvalidSymbol;
+        g_scan_static_ptr[dev] = p;
+    }
+    *out = g_scan_static_ptr[dev];
+    return 0;
+}
+
+}  // namespace
+
+COL_API int col_exclusive_scan_u32_static(uint32_t* data, uint64_t n, uint64_t* total_out, void* stream) {
+    if (!data && n) return COL_ERR_BAD_ARG;
+    if (n > COL_SCAN_STATIC_MAX_N) {
+        fprintf(stderr, "col_exclusive_scan_u32_static: n = %llu exceeds COL_SCAN_STATIC_MAX_N = %llu "
+                        "(the built-in scratch array); use col_exclusive_scan_u32 with caller scratch\n",
+                (unsigned long long)n, (unsigned long long)COL_SCAN_STATIC_MAX_N);
+        return COL_ERR_TOO_LARGE;
+    }
+    cudaStream_t s = col_stream(stream);
+    if (n == 0) {
+        if (total_out) COL_CUDA(cudaMemsetAsync(total_out, 0, sizeof(uint64_t), s));
+        return 0;
+    }
+    void* scratch = nullptr;
+    const int rc = scan_static_address(&scratch);
+    if (rc) return rc;
+    const uint64_t tiles = (n + SCAN_TILE - 1) / SCAN_TILE;
     COL_CUDA(cudaMemsetAsync(scratch, 0, SCAN_STATUS_OFF + (size_t)tiles * sizeof(uint64_t), s));
     unsigned* ticket = reinterpret_cast<unsigned*>(scratch);
     uint64_t* status = reinterpret_cast<uint64_t*>(reinterpret_cast<char*>(scratch) + SCAN_STATUS_OFF);

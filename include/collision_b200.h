@@ -92,6 +92,16 @@ int col_morton(uint32_t* codes, uint32_t* ids, const void* coords4, const void* 
 size_t col_scan_scratch_bytes(uint64_t n);
 int col_exclusive_scan_u32(uint32_t* data, uint64_t n, uint64_t* total_out, void* scratch,
                            void* stream);
+/* The same scan with NO caller scratch and no allocation of any kind (no cudaMalloc / cudaFree,
+ * safe under CUDA graph capture and in loops that must not allocate).  This entry point has no
+ * counterpart in the reference.  The ticket
+ * and status words live in a 16,640-byte device array built into the library (every GPU that loads
+ * the library holds it until exit), which limits n to COL_SCAN_STATIC_MAX_N values: larger n is
+ * refused with COL_ERR_TOO_LARGE and a message on stderr.  All calls on one GPU share the array:
+ * calls that overlap on the GPU (different streams or threads) race -- serialise them.  Results
+ * are identical to col_exclusive_scan_u32 (integer arithmetic, bit-exact). */
+#define COL_SCAN_STATIC_MAX_N (1ull << 24)
+int col_exclusive_scan_u32_static(uint32_t* data, uint64_t n, uint64_t* total_out, void* stream);
 
 /* ------------------------------------------------------------------- sort
  * Replaces RadixSorter.sort (collision/radix.py:118-170; block_sort / scatter,
