@@ -68,7 +68,10 @@ SIGNATURES = {
     "col_shard_list_bytes": (_sz, [_u32]),
     "col_shard_build_windows": (_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _int, _u32, _u32, _u32, _vp, _u32, _vp]),
     "col_shard_top": (_int, [_vp, _u32, _u32, _u32, _vp, _vp, _vp, _vp, _vp, _vp, _int, _u32, _vp]),
-    "col_shard_halo": (_int, [_vp, _u32, _u32, _u32, _vp, _vp, _vp, _int, _vp, _vp, _u32, _vp, _vp, _vp, _u32, _u32, _u32, _vp]),
+    "col_shard_halo": (_int, [_vp, _u32, _u32, _u32, _vp, _vp, _vp, _int, _vp, _vp, _u32, _vp, _vp, _vp, _u32, _u32, _u32,
+                              _vp, _vp, _vp]),
+    "col_shard_sort_scratch_bytes": (_sz, [_u64]),
+    "col_shard_sort": (_int, [_vp, _u32, _u32, _u32, _u32, _vp, _vp, _vp, _vp, _vp]),
     "col_fill_u32": (_int, [_vp, _u32, _u64, _vp]),
     "col_range": (_int, [_vp, _u64, _vp]),
     "col_copy": (_int, [_vp, _vp, _u64, _vp]),

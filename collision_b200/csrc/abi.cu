@@ -1,5 +1,5 @@
 // abi.cu -- version / build information of libcollision_b200.so
 #include "common.cuh"
 
-COL_API int col_abi_version(void) { return 1; }
+COL_API int col_abi_version(void) { return 2; }
 COL_API int col_built_arch(void) { return 100; }

@@ -511,6 +511,8 @@ leaf_bounds_kernel(T* __restrict__ bounds, const T* __restrict__ coords, const T
 // owners' buffers are mapped through CUDA IPC, ipc.cu).
 template <typename T> struct PackedItem {
     uint32_t self, lo, hi, pad;   // node index (leaf: leaf_start + position), covered sorted positions [lo, hi]
+    uint32_t code[4];             // sorted codes at lo - 1, lo, hi, hi + 1 (0 where there is no such position): with the
+                                  // sharded sort the other ranks do not hold them, and the top pass reads nothing else
     T box[6];                     // exact box: lo xyz, hi xyz
 };
 constexpr uint32_t PACK_HEADER = 64;   // bytes: {count, overflow, ...} in front of a rank's packed items
@@ -519,7 +521,8 @@ constexpr uint32_t PACK_HEADER = 64;   // bytes: {count, overflow, ...} in front
 template <typename T>
 __global__ void __launch_bounds__(256)
 pack_items_kernel(const uint32_t* __restrict__ items, const col_node* __restrict__ nodes, const T* __restrict__ bounds,
-                  unsigned char* __restrict__ packed, uint32_t cap, uint32_t n, uint32_t leaf_begin, uint32_t leaf_end) {
+                  const uint32_t* __restrict__ codes, unsigned char* __restrict__ packed, uint32_t cap, uint32_t n,
+                  uint32_t leaf_begin, uint32_t leaf_end) {
     const uint32_t s = leaf_begin + blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= leaf_end) return;
     const uint32_t self = items[s];
@@ -541,10 +544,35 @@ pack_items_kernel(const uint32_t* __restrict__ items, const col_node* __restrict
         it.hi = rec.y;
     }
     it.pad = 0;
+    it.code[0] = it.lo > 0 ? __ldg(codes + it.lo - 1) : 0u;
+    it.code[1] = __ldg(codes + it.lo);
+    it.code[2] = __ldg(codes + it.hi);
+    it.code[3] = it.hi < leaf_start ? __ldg(codes + it.hi + 1) : 0u;
     const T* b = bounds + (size_t)self * 8;
     it.box[0] = b[0]; it.box[1] = b[1]; it.box[2] = b[2];
     it.box[3] = b[4]; it.box[4] = b[5]; it.box[5] = b[6];
     reinterpret_cast<PackedItem<T>*>(packed + PACK_HEADER)[k] = it;
+}
+
+// The codes at the ends of the other ranks' roots -> their places in this rank's array of sorted codes
+// (with the sharded sort it holds the rank's own part only).  Every position the top pass reads is the
+// lo - 1 / lo / hi / hi + 1 of some root: a spanning node's range ends where two of its descendants' do.
+template <typename T>
+__global__ void __launch_bounds__(256)
+scatter_root_codes_kernel(const unsigned char* __restrict__ gathered, uint32_t cap, uint32_t world, uint32_t my_rank,
+                          uint32_t* __restrict__ codes, uint32_t n) {
+    const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t r = (uint32_t)(t / cap), j = (uint32_t)(t % cap);
+    if (r >= world || r == my_rank) return;
+    const size_t stride = PACK_HEADER + (size_t)cap * sizeof(PackedItem<T>);
+    const unsigned char* theirs = gathered + r * stride;
+    if (j >= min(*reinterpret_cast<const uint32_t*>(theirs), cap)) return;
+    const PackedItem<T>* it = reinterpret_cast<const PackedItem<T>*>(theirs + PACK_HEADER) + j;
+    const uint32_t lo = it->lo, hi = it->hi;
+    if (lo > 0) codes[lo - 1] = it->code[0];
+    codes[lo] = it->code[1];
+    codes[hi] = it->code[2];
+    if (hi + 1 < n) codes[hi + 1] = it->code[3];
 }
 
 // top pass over the gathered roots of ALL ranks (replicated on every rank)
@@ -652,8 +680,9 @@ __device__ __forceinline__ uint4 ld_cg_u4(const uint4* p) {
 __global__ void __launch_bounds__(256)
 halo_fetch_kernel(const uint2* __restrict__ list, const uint32_t* __restrict__ list_hdr, uint32_t list_cap,
                   const unsigned long long* __restrict__ wide_table, const unsigned long long* __restrict__ bounds_table,
-                  const uint32_t* __restrict__ win_edges, uint32_t world, unsigned char* __restrict__ wide,
-                  unsigned char* __restrict__ bounds, uint32_t box_bytes, uint32_t n) {
+                  const unsigned long long* __restrict__ ids_table, const uint32_t* __restrict__ win_edges,
+                  uint32_t world, unsigned char* __restrict__ wide, unsigned char* __restrict__ bounds,
+                  uint32_t* __restrict__ ids, uint32_t box_bytes, uint32_t n) {
     const uint32_t count = min(list_hdr[0], list_cap);
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t leaf_start = n - 1;
@@ -676,6 +705,10 @@ halo_fetch_kernel(const uint2* __restrict__ list, const uint32_t* __restrict__ l
         for (uint32_t k = lane; k < nbox16; k += 32) {
             const size_t off = (size_t)(leaf_start + ent.x) * box_bytes + (size_t)k * 16;
             *reinterpret_cast<uint4*>(bounds + off) = ld_cg_u4(reinterpret_cast<const uint4*>(src_b + off));
+        }
+        if (ids_table) {   // sharded sort: the sphere ids of those leaves are the owner's to give, too
+            const uint32_t* src_i = reinterpret_cast<const uint32_t*>(ids_table[owner]);
+            for (uint32_t k = ent.x + lane; k <= ent.y; k += 32) ids[k] = ld_relaxed_u32(src_i + k);
         }
     }
 }
@@ -807,13 +840,13 @@ COL_API int col_shard_build_windows(const uint32_t* codes_sorted, const uint32_t
         build_refit_kernel<float, true><<<blocks, BR_WINDOW, 0, s>>>(
             codes_sorted, ids_sorted, (col_node*)nodes, (unsigned char*)wide, flags, items, (float*)bounds,
             (const float*)coords4, (const float*)radii, (const float*)scene2x4, n, win_begin);
-        pack_items_kernel<float><<<pblocks, 256, 0, s>>>(items, (const col_node*)nodes, (const float*)bounds,
+        pack_items_kernel<float><<<pblocks, 256, 0, s>>>(items, (const col_node*)nodes, (const float*)bounds, codes_sorted,
                                                          (unsigned char*)packed, cap, n, leaf_begin, leaf_end);
     } else {
         build_refit_kernel<double, true><<<blocks, BR_WINDOW, 0, s>>>(
             codes_sorted, ids_sorted, (col_node*)nodes, (unsigned char*)wide, flags, items, (double*)bounds,
             (const double*)coords4, (const double*)radii, (const double*)scene2x4, n, win_begin);
-        pack_items_kernel<double><<<pblocks, 256, 0, s>>>(items, (const col_node*)nodes, (const double*)bounds,
+        pack_items_kernel<double><<<pblocks, 256, 0, s>>>(items, (const col_node*)nodes, (const double*)bounds, codes_sorted,
                                                           (unsigned char*)packed, cap, n, leaf_begin, leaf_end);
     }
     COL_CHECK_LAUNCH();
@@ -821,7 +854,7 @@ COL_API int col_shard_build_windows(const uint32_t* codes_sorted, const uint32_t
 }
 
 COL_API int col_shard_top(const void* gathered, uint32_t cap, uint32_t world, uint32_t my_rank,
-                          const uint32_t* codes_sorted, void* nodes, void* wide, uint32_t* flags, void* bounds,
+                          uint32_t* codes_sorted, void* nodes, void* wide, uint32_t* flags, void* bounds,
                           const void* scene2x4, int dtype, uint32_t n, void* stream) {
     if (!gathered || !codes_sorted || !nodes || !wide || !flags || !bounds || !scene2x4 || cap == 0 || world == 0 ||
         my_rank >= world)
@@ -829,6 +862,12 @@ COL_API int col_shard_top(const void* gathered, uint32_t cap, uint32_t world, ui
     if (dtype != COL_F32 && dtype != COL_F64) return COL_ERR_UNSUPPORTED;
     cudaStream_t s = col_stream(stream);
     const unsigned blocks = col_blocks((uint64_t)cap * world, 256);
+    // (the same values the replicated sort left there; the only ones this rank has after the sharded sort)
+    if (dtype == COL_F32)
+        scatter_root_codes_kernel<float><<<blocks, 256, 0, s>>>((const unsigned char*)gathered, cap, world, my_rank, codes_sorted, n);
+    else
+        scatter_root_codes_kernel<double><<<blocks, 256, 0, s>>>((const unsigned char*)gathered, cap, world, my_rank, codes_sorted, n);
+    COL_CHECK_LAUNCH();
     if (dtype == COL_F32)
         top_packed_kernel<float><<<blocks, 256, 0, s>>>((const unsigned char*)gathered, cap, world, my_rank, codes_sorted,
                                                         (col_node*)nodes, (unsigned char*)wide, flags, (float*)bounds,
@@ -844,9 +883,10 @@ COL_API int col_shard_top(const void* gathered, uint32_t cap, uint32_t world, ui
 COL_API int col_shard_halo(const void* gathered, uint32_t cap, uint32_t world, uint32_t my_rank, void* wide, void* bounds,
                            const void* scene2x4, int dtype, uint32_t* flags, void* list, uint32_t list_cap,
                            const uint64_t* wide_table, const uint64_t* bounds_table, const uint32_t* win_edges,
-                           uint32_t n, uint32_t leaf_begin, uint32_t leaf_end, void* stream) {
+                           uint32_t n, uint32_t leaf_begin, uint32_t leaf_end, const uint64_t* ids_table,
+                           uint32_t* ids_sorted, void* stream) {
     if (!gathered || !wide || !bounds || !scene2x4 || !flags || !list || !wide_table || !bounds_table || !win_edges ||
-        cap == 0 || list_cap == 0 || my_rank >= world)
+        cap == 0 || list_cap == 0 || my_rank >= world || (ids_table && !ids_sorted))
         return COL_ERR_BAD_ARG;
     if (dtype != COL_F32 && dtype != COL_F64) return COL_ERR_UNSUPPORTED;
     cudaStream_t s = col_stream(stream);
@@ -865,8 +905,9 @@ COL_API int col_shard_halo(const void* gathered, uint32_t cap, uint32_t world, u
                                                           asked, entries, hdr, list_cap, n, leaf_begin, leaf_end);
     COL_CHECK_LAUNCH();
     halo_fetch_kernel<<<COL_NUM_SMS * 8, 256, 0, s>>>(entries, hdr, list_cap, (const unsigned long long*)wide_table,
-                                                      (const unsigned long long*)bounds_table, win_edges, world,
-                                                      (unsigned char*)wide, (unsigned char*)bounds,
+                                                      (const unsigned long long*)bounds_table,
+                                                      (const unsigned long long*)ids_table, win_edges, world,
+                                                      (unsigned char*)wide, (unsigned char*)bounds, ids_sorted,
                                                       dtype == COL_F64 ? 64u : 32u, n);
     COL_CHECK_LAUNCH();
     return 0;

@@ -54,8 +54,9 @@ constexpr int HIST_ITEMS = 16;  // keys per thread per iteration
 template <typename K>
 __global__ void __launch_bounds__(HIST_THREADS)
 histogram_kernel(const K* __restrict__ keys, uint64_t n, uint32_t* __restrict__ ghist, uint32_t shift0,
-                 uint32_t bits, uint32_t npass) {
+                 uint32_t bits, uint32_t npass, const uint32_t* __restrict__ range) {
     __shared__ uint32_t sh[MAX_PASSES * RADIX];
+    if (range) n = range[1];   // {offset, count} on the device: the host sized the launch for an upper bound
     for (int i = threadIdx.x; i < MAX_PASSES * RADIX; i += HIST_THREADS) sh[i] = 0;
     __syncthreads();
     const uint32_t mask = (1u << bits) - 1;
@@ -291,11 +292,16 @@ __device__ __forceinline__ void onesweep_tile(const K* __restrict__ keys_in, K* 
     }
 }
 
-template <typename K, bool HAS_VALUES>
+// RANGE (the sharded sort, col_shard_sort): the number of keys is only known on the device --
+// range = {offset, count} -- so the host launches a fixed grid and every block takes tiles by ticket
+// until they run out; `place` (the last pass) shifts the output by `offset`, the place of the
+// sorted run in the whole array.
+template <typename K, bool HAS_VALUES, bool RANGE>
 __global__ void __launch_bounds__(SORT_THREADS, COL_SORT_CTAS)
 onesweep_kernel(const K* __restrict__ keys_in, K* __restrict__ keys_out, const uint32_t* __restrict__ vals_in,
                 uint32_t* __restrict__ vals_out, uint32_t n, const uint32_t* __restrict__ digit_base,
-                uint32_t* __restrict__ status, unsigned* ticket, uint32_t shift, uint32_t mask, uint32_t bits) {
+                uint32_t* __restrict__ status, unsigned* ticket, uint32_t shift, uint32_t mask, uint32_t bits,
+                const uint32_t* __restrict__ range, uint32_t place) {
     constexpr int ITEMS = Tile<K>::ITEMS;
     constexpr int TILE = SORT_THREADS * ITEMS;
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -305,16 +311,27 @@ onesweep_kernel(const K* __restrict__ keys_in, K* __restrict__ keys_out, const u
     __shared__ unsigned s_tile;
 
     uint32_t* s_whist = reinterpret_cast<uint32_t*>(smem_raw + sizeof(K) * skewed(TILE));
-    if (threadIdx.x == 0) s_tile = atomicAdd(ticket, 1u);
-    for (int i = threadIdx.x; i < SORT_WARPS * RADIX; i += SORT_THREADS) s_whist[i] = 0;
-    __syncthreads();
-    const unsigned tile = s_tile;
-    if ((uint64_t)(tile + 1) * TILE <= n)
-        onesweep_tile<K, ITEMS, true, HAS_VALUES>(keys_in, keys_out, vals_in, vals_out, n, digit_base, status, shift,
-                                                  mask, bits, tile, smem_raw, s_digit_start, s_global_off, s_scan_warp);
-    else
-        onesweep_tile<K, ITEMS, false, HAS_VALUES>(keys_in, keys_out, vals_in, vals_out, n, digit_base, status, shift,
-                                                   mask, bits, tile, smem_raw, s_digit_start, s_global_off, s_scan_warp);
+    if (RANGE) {
+        n = range[1];
+        if (place) {
+            keys_out += range[0];
+            if (HAS_VALUES) vals_out += range[0];
+        }
+    }
+    do {
+        if (threadIdx.x == 0) s_tile = atomicAdd(ticket, 1u);
+        for (int i = threadIdx.x; i < SORT_WARPS * RADIX; i += SORT_THREADS) s_whist[i] = 0;
+        __syncthreads();
+        const unsigned tile = s_tile;
+        if (RANGE && (uint64_t)tile * TILE >= n) return;
+        if ((uint64_t)(tile + 1) * TILE <= n)
+            onesweep_tile<K, ITEMS, true, HAS_VALUES>(keys_in, keys_out, vals_in, vals_out, n, digit_base, status, shift,
+                                                      mask, bits, tile, smem_raw, s_digit_start, s_global_off, s_scan_warp);
+        else
+            onesweep_tile<K, ITEMS, false, HAS_VALUES>(keys_in, keys_out, vals_in, vals_out, n, digit_base, status, shift,
+                                                       mask, bits, tile, smem_raw, s_digit_start, s_global_off, s_scan_warp);
+        if (RANGE) __syncthreads();   // the tile's shared memory is reused by the next one
+    } while (RANGE);
 }
 
 template <typename K, bool HAS_VALUES> constexpr size_t onesweep_smem() {
@@ -356,7 +373,10 @@ __global__ void __launch_bounds__(256) iota_kernel(uint32_t* p, uint32_t n) {
 
 template <typename K>
 int run_passes(const K* keys_in, K* keys_out, const uint32_t* vals_in, uint32_t* vals_out, uint32_t n,
-               uint32_t shift0, uint32_t bits, uint32_t npass, char* scratch, const SortLayout& L, cudaStream_t s) {
+               uint32_t shift0, uint32_t bits, uint32_t npass, char* scratch, const SortLayout& L, cudaStream_t s,
+               const uint32_t* range = nullptr) {
+    // range (device {offset, count}, see onesweep_kernel): n is then an upper bound, every buffer is read and
+    // written from its start, except that the last pass writes at keys_out / vals_out + offset
     uint32_t* ghist = reinterpret_cast<uint32_t*>(scratch + L.ghist);
     unsigned* tickets = reinterpret_cast<unsigned*>(scratch + L.tickets);
     K* tmp_keys = reinterpret_cast<K*>(scratch + L.tmp_keys);
@@ -368,7 +388,7 @@ int run_passes(const K* keys_in, K* keys_out, const uint32_t* vals_in, uint32_t*
     {
         uint64_t want = ((uint64_t)n + HIST_THREADS * HIST_ITEMS - 1) / (HIST_THREADS * HIST_ITEMS);
         unsigned blocks = (unsigned)(want > COL_NUM_SMS * 4 ? COL_NUM_SMS * 4 : want);
-        histogram_kernel<K><<<blocks, HIST_THREADS, 0, s>>>(keys_in, n, ghist, shift0, bits, npass);
+        histogram_kernel<K><<<blocks, HIST_THREADS, 0, s>>>(keys_in, n, ghist, shift0, bits, npass, range);
         COL_CHECK_LAUNCH();
         digit_base_kernel<<<npass, RADIX, 0, s>>>(ghist);
         COL_CHECK_LAUNCH();
@@ -381,7 +401,7 @@ int run_passes(const K* keys_in, K* keys_out, const uint32_t* vals_in, uint32_t*
     // 2^20, so the ballot pass stays the default; the alternative is kept for A/B runs.
     auto aligned32 = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 31u) == 0; };
     static const bool column = getenv("COL_SORT_COLUMN") != nullptr;
-    const bool col = sizeof(K) == 4 && column && aligned32(keys_in) && aligned32(keys_out) && aligned32(tmp_keys) &&
+    const bool col = sizeof(K) == 4 && column && !range && aligned32(keys_in) && aligned32(keys_out) && aligned32(tmp_keys) &&
                      (!has_vals || (aligned32(vals_in) && aligned32(vals_out) && aligned32(tmp_vals)));
     for (uint32_t p = 0; p < npass; p++) {
         // the last pass lands in *_out; earlier ones alternate tmp/out backwards from there
@@ -390,6 +410,15 @@ int run_passes(const K* keys_in, K* keys_out, const uint32_t* vals_in, uint32_t*
         K* kout = to_out ? keys_out : tmp_keys;
         const uint32_t* vin = p == 0 ? vals_in : (to_out ? tmp_vals : vals_out);
         uint32_t* vout = to_out ? vals_out : tmp_vals;
+        if (range) {
+            // the input (the collected keys: scratch of the caller, writable) and tmp take turns, so that
+            // *_out is written once, by the last pass, and only inside [offset, offset + count)
+            const bool even = (p & 1u) == 0, last = p + 1 == npass;
+            kin = even ? keys_in : tmp_keys;
+            vin = even ? vals_in : tmp_vals;
+            kout = last ? keys_out : (even ? tmp_keys : const_cast<K*>(keys_in));
+            vout = last ? vals_out : (even ? tmp_vals : const_cast<uint32_t*>(vals_in));
+        }
         uint32_t* status = reinterpret_cast<uint32_t*>(scratch + L.status + L.status_bytes * p);
         if (col) {
             const int rc = has_vals
@@ -400,16 +429,24 @@ int run_passes(const K* keys_in, K* keys_out, const uint32_t* vals_in, uint32_t*
             if (rc) return rc;
             continue;
         }
-        if (has_vals) {
+        if (range) {   // (key/value pairs only)
             constexpr size_t smem = onesweep_smem<K, true>();
-            COL_CUDA(cudaFuncSetAttribute(onesweep_kernel<K, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-            onesweep_kernel<K, true><<<(unsigned)L.tiles, SORT_THREADS, smem, s>>>(
-                kin, kout, vin, vout, n, ghist + p * RADIX, status, tickets + p, shift0 + p * bits, mask, bits);
+            COL_CUDA(cudaFuncSetAttribute(onesweep_kernel<K, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            const unsigned resident = COL_NUM_SMS * COL_SORT_CTAS;
+            const unsigned grid = L.tiles < resident ? (unsigned)L.tiles : resident;
+            onesweep_kernel<K, true, true><<<grid, SORT_THREADS, smem, s>>>(
+                kin, kout, vin, vout, n, ghist + p * RADIX, status, tickets + p, shift0 + p * bits, mask, bits, range,
+                p + 1 == npass ? 1u : 0u);
+        } else if (has_vals) {
+            constexpr size_t smem = onesweep_smem<K, true>();
+            COL_CUDA(cudaFuncSetAttribute(onesweep_kernel<K, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            onesweep_kernel<K, true, false><<<(unsigned)L.tiles, SORT_THREADS, smem, s>>>(
+                kin, kout, vin, vout, n, ghist + p * RADIX, status, tickets + p, shift0 + p * bits, mask, bits, nullptr, 0u);
         } else {
             constexpr size_t smem = onesweep_smem<K, false>();
-            COL_CUDA(cudaFuncSetAttribute(onesweep_kernel<K, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-            onesweep_kernel<K, false><<<(unsigned)L.tiles, SORT_THREADS, smem, s>>>(
-                kin, kout, nullptr, nullptr, n, ghist + p * RADIX, status, tickets + p, shift0 + p * bits, mask, bits);
+            COL_CUDA(cudaFuncSetAttribute(onesweep_kernel<K, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            onesweep_kernel<K, false, false><<<(unsigned)L.tiles, SORT_THREADS, smem, s>>>(
+                kin, kout, nullptr, nullptr, n, ghist + p * RADIX, status, tickets + p, shift0 + p * bits, mask, bits, nullptr, 0u);
         }
         COL_CHECK_LAUNCH();
     }
@@ -469,4 +506,215 @@ COL_API int col_radix_pass(const void* keys_in, void* keys_out, const void* vals
     if (radix_bits == 0 || radix_bits > RADIX_BITS || (pass + 1) * radix_bits > key_bytes * 8) return COL_ERR_BAD_ARG;
     return sort_impl(keys_in, keys_out, vals_in, vals_out, n, key_bytes, value_bytes, pass * radix_bits, radix_bits, 1,
                      scratch, col_stream(stream));
+}
+
+// ================================================================ sharded sort (multi-GPU)
+// col_shard_sort: the part [pos_lo, pos_hi] of the stably sorted order of ALL n codes, without
+// sorting the rest (collision_b200/sharded.py, mode "sharded_build": a rank only needs the sorted
+// leaves of its own windows).  Every rank holds all n codes (4 B per sphere, all-gathered) and
+//   1. counts their TOP digit (bits [end_bit - 8, end_bit)): the 256 bucket starts in the sorted order;
+//   2. picks the buckets [d_lo, d_hi] that cover positions pos_lo..pos_hi: they hold `count` codes and
+//      start at position `offset` (range_out = {offset, count, d_lo, d_hi}, all on the device -- no
+//      host round trip, the step stays capturable);
+//   3. collects (code, index) of exactly those codes, in input order (stable compaction: tiles in
+//      ticket order, one 64-bit look-back word per tile);
+//   4. sorts the collected pairs on all end_bit bits; the last pass writes them at
+//      codes_sorted / ids_sorted + offset, their place in the order of the whole scene.
+// Everything before `offset` belongs to smaller buckets, everything after to larger ones, and the
+// LSD passes are stable, so positions [offset, offset + count) come out exactly as the full sort
+// writes them.  Traffic: 8 B per code (count + collect) + 68 B per collected pair.  A scene that
+// sits in one bucket degrades to the full sort (still correct).
+namespace {
+
+constexpr int COLLECT_THREADS = 256;
+constexpr int COLLECT_VECS = 8;
+constexpr int COLLECT_TILE = COLLECT_THREADS * COLLECT_VECS * 4;   // 8192 codes
+constexpr int COLLECT_WARP_ITEMS = 32 * COLLECT_VECS * 4;
+
+// starts = exclusive bucket starts (256); range_out = {offset, count, d_lo, d_hi}
+__global__ void __launch_bounds__(RADIX) select_buckets_kernel(const uint32_t* __restrict__ starts, uint32_t n,
+                                                               uint32_t pos_lo, uint32_t pos_hi,
+                                                               uint32_t* __restrict__ range_out) {
+    __shared__ uint32_t s_lo, s_hi;
+    if (threadIdx.x == 0) { s_lo = 0; s_hi = 0; }
+    __syncthreads();
+    // the bucket that holds position p = the last one that starts at or before p (empty buckets share
+    // their start with the next one, so the last such bucket is never empty for p < n)
+    const uint32_t d = threadIdx.x, st = starts[d];
+    if (st <= pos_lo) atomicMax(&s_lo, d);
+    if (st <= pos_hi) atomicMax(&s_hi, d);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const uint32_t off = starts[s_lo], end = s_hi + 1 < RADIX ? starts[s_hi + 1] : n;
+        range_out[0] = off;
+        range_out[1] = end - off;
+        range_out[2] = s_lo;
+        range_out[3] = s_hi;
+    }
+}
+
+__global__ void __launch_bounds__(COLLECT_THREADS)
+collect_kernel(const uint32_t* __restrict__ codes, uint32_t n, uint32_t shift, uint32_t mask, const uint32_t* __restrict__ range,
+               uint32_t* __restrict__ keys_out, uint32_t* __restrict__ ids_out, unsigned* ticket, uint64_t* status) {
+    __shared__ unsigned s_tile;
+    __shared__ uint32_t s_warp_total[COLLECT_THREADS / 32];
+    __shared__ uint32_t s_tile_prefix;
+    if (threadIdx.x == 0) s_tile = atomicAdd(ticket, 1u);
+    __syncthreads();
+    const unsigned tile = s_tile;
+    const uint32_t tile_base = tile * (uint32_t)COLLECT_TILE;
+    const unsigned warp = threadIdx.x >> 5, lane = lane_id();
+    const uint32_t warp_base = tile_base + warp * COLLECT_WARP_ITEMS;
+    const bool full = (uint64_t)tile_base + COLLECT_TILE <= n;
+    const uint32_t d_lo = range[2], span = range[3] - d_lo;
+
+    uint4 v[COLLECT_VECS];
+    uint32_t sel[COLLECT_VECS];     // 4 bits: which of the four codes of the vector are collected
+    uint32_t excl[COLLECT_VECS];    // collected before mine inside the warp's part of the tile
+    uint32_t row_base = 0;
+#pragma unroll
+    for (int k = 0; k < COLLECT_VECS; k++) {
+        const uint32_t e = warp_base + (uint32_t)(k * 32 + lane) * 4;
+        if (full) {
+            v[k] = ld_stream_u4(reinterpret_cast<const uint4*>(codes + e));
+        } else {
+            v[k].x = e + 0 < n ? codes[e + 0] : 0u;
+            v[k].y = e + 1 < n ? codes[e + 1] : 0u;
+            v[k].z = e + 2 < n ? codes[e + 2] : 0u;
+            v[k].w = e + 3 < n ? codes[e + 3] : 0u;
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < COLLECT_VECS; k++) {
+        const uint32_t e = warp_base + (uint32_t)(k * 32 + lane) * 4;
+        uint32_t m = 0;
+        m |= ((((v[k].x >> shift) & mask) - d_lo) <= span && (full || e + 0 < n)) ? 1u : 0u;
+        m |= ((((v[k].y >> shift) & mask) - d_lo) <= span && (full || e + 1 < n)) ? 2u : 0u;
+        m |= ((((v[k].z >> shift) & mask) - d_lo) <= span && (full || e + 2 < n)) ? 4u : 0u;
+        m |= ((((v[k].w >> shift) & mask) - d_lo) <= span && (full || e + 3 < n)) ? 8u : 0u;
+        sel[k] = m;
+        const uint32_t c = (uint32_t)__popc(m);
+        uint32_t inc = c;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t up = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += up;
+        }
+        excl[k] = row_base + inc - c;
+        row_base += __shfl_sync(0xffffffffu, inc, 31);
+    }
+    if (lane == 0) s_warp_total[warp] = row_base;
+    __syncthreads();
+    uint32_t warp_prefix = 0, tile_total = 0;
+#pragma unroll
+    for (int w = 0; w < COLLECT_THREADS / 32; w++) {
+        const uint32_t t = s_warp_total[w];
+        if (w < (int)warp) warp_prefix += t;
+        tile_total += t;
+    }
+    // decoupled look-back by warp 0 over {flag:2, count:62} words, 32 predecessors per step
+    if (warp == 0) {
+        constexpr uint64_t PARTIAL = 1ull << 62, INCLUSIVE = 2ull << 62, VALUE = (1ull << 62) - 1;
+        uint64_t prefix = 0;
+        if (tile == 0) {
+            if (lane == 0) st_relaxed_u64(status, INCLUSIVE | tile_total);
+        } else {
+            if (lane == 0) st_relaxed_u64(status + tile, PARTIAL | tile_total);
+            int64_t look = (int64_t)tile - 1 - lane;
+            while (true) {
+                uint64_t st = INCLUSIVE;
+                if (look >= 0) {
+                    do { st = ld_relaxed_u64(status + look); } while ((st >> 62) == 0);
+                }
+                const unsigned inc_mask = __ballot_sync(0xffffffffu, (st >> 62) == 2);
+                const unsigned first = inc_mask ? (unsigned)__ffs(inc_mask) - 1 : 31u;
+                uint64_t c = (lane <= first) ? (st & VALUE) : 0;
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+                prefix += c;
+                if (inc_mask) break;
+                look -= 32;
+            }
+            if (lane == 0) st_relaxed_u64(status + tile, INCLUSIVE | (prefix + tile_total));
+        }
+        if (lane == 0) s_tile_prefix = (uint32_t)prefix;
+    }
+    __syncthreads();
+    const uint32_t base = s_tile_prefix + warp_prefix;
+#pragma unroll
+    for (int k = 0; k < COLLECT_VECS; k++) {
+        const uint32_t e = warp_base + (uint32_t)(k * 32 + lane) * 4;
+        uint32_t dst = base + excl[k];
+        const uint32_t m = sel[k];
+#ifdef COL_DEBUG
+        if (m && dst + __popc(m) > range[1]) __trap();   // more collected than the buckets hold
+#endif
+        if (m & 1u) { keys_out[dst] = v[k].x; ids_out[dst] = e + 0; dst++; }
+        if (m & 2u) { keys_out[dst] = v[k].y; ids_out[dst] = e + 1; dst++; }
+        if (m & 4u) { keys_out[dst] = v[k].z; ids_out[dst] = e + 2; dst++; }
+        if (m & 8u) { keys_out[dst] = v[k].w; ids_out[dst] = e + 3; dst++; }
+    }
+}
+
+struct ShardSortLayout {
+    size_t hist, ticket, status, keys, vals, sort, total;
+    uint64_t tiles;
+};
+
+ShardSortLayout shard_sort_layout(uint64_t n) {
+    ShardSortLayout L;
+    L.tiles = (n + COLLECT_TILE - 1) / COLLECT_TILE;
+    if (L.tiles == 0) L.tiles = 1;
+    size_t off = 0;
+    L.hist = off; off += align_up(sizeof(uint32_t) * RADIX);
+    L.ticket = off; off += align_up(sizeof(uint32_t));
+    L.status = off; off += align_up(sizeof(uint64_t) * L.tiles);
+    L.keys = off; off += align_up((size_t)n * 4);
+    L.vals = off; off += align_up((size_t)n * 4);
+    L.sort = off; off += sort_layout(n, 4, 4).total;
+    L.total = off;
+    return L;
+}
+
+}  // namespace
+
+COL_API size_t col_shard_sort_scratch_bytes(uint64_t n) { return shard_sort_layout(n).total; }
+
+COL_API int col_shard_sort(const uint32_t* codes, uint32_t n, uint32_t pos_lo, uint32_t pos_hi, uint32_t end_bit,
+                           uint32_t* codes_sorted, uint32_t* ids_sorted, uint32_t* range_out, void* scratch_v,
+                           void* stream) {
+    if (!codes || !codes_sorted || !ids_sorted || !range_out || !scratch_v) return COL_ERR_BAD_ARG;
+    if (n == 0 || pos_lo > pos_hi || pos_lo >= n) return COL_ERR_BAD_ARG;
+    if (n > (1u << 30)) return COL_ERR_TOO_LARGE;
+    if (end_bit == 0 || end_bit > 32) end_bit = 32;
+    if (pos_hi >= n) pos_hi = n - 1;
+    if ((reinterpret_cast<uintptr_t>(codes) & 15u) != 0) return COL_ERR_BAD_ARG;   // 128-bit loads
+    cudaStream_t s = col_stream(stream);
+    char* scratch = reinterpret_cast<char*>(scratch_v);
+    const ShardSortLayout L = shard_sort_layout(n);
+    uint32_t* hist = reinterpret_cast<uint32_t*>(scratch + L.hist);
+    unsigned* ticket = reinterpret_cast<unsigned*>(scratch + L.ticket);
+    uint64_t* status = reinterpret_cast<uint64_t*>(scratch + L.status);
+    uint32_t* keys = reinterpret_cast<uint32_t*>(scratch + L.keys);
+    uint32_t* vals = reinterpret_cast<uint32_t*>(scratch + L.vals);
+    const uint32_t top_shift = end_bit > RADIX_BITS ? end_bit - RADIX_BITS : 0;
+    const uint32_t top_bits = end_bit > RADIX_BITS ? RADIX_BITS : end_bit;
+    COL_CUDA(cudaMemsetAsync(scratch, 0, L.keys, s));   // histogram, ticket, look-back words
+    {
+        const uint64_t want = ((uint64_t)n + HIST_THREADS * HIST_ITEMS - 1) / (HIST_THREADS * HIST_ITEMS);
+        const unsigned blocks = (unsigned)(want > COL_NUM_SMS * 4 ? COL_NUM_SMS * 4 : want);
+        histogram_kernel<uint32_t><<<blocks, HIST_THREADS, 0, s>>>(codes, n, hist, top_shift, top_bits, 1, nullptr);
+        COL_CHECK_LAUNCH();
+        digit_base_kernel<<<1, RADIX, 0, s>>>(hist);
+        COL_CHECK_LAUNCH();
+    }
+    select_buckets_kernel<<<1, RADIX, 0, s>>>(hist, n, pos_lo, pos_hi, range_out);
+    COL_CHECK_LAUNCH();
+    collect_kernel<<<(unsigned)L.tiles, COLLECT_THREADS, 0, s>>>(codes, n, top_shift, (1u << top_bits) - 1, range_out, keys, vals,
+                                                                ticket, status);
+    COL_CHECK_LAUNCH();
+    const uint32_t npass = (end_bit + RADIX_BITS - 1) / RADIX_BITS;
+    const SortLayout SL = sort_layout(n, 4, 4);
+    return run_passes<uint32_t>(keys, codes_sorted, vals, ids_sorted, n, 0, RADIX_BITS, npass, scratch + L.sort, SL, s,
+                                range_out);
 }

@@ -21,7 +21,7 @@ import torch.distributed as dist
 from numpy import dtype
 
 from . import _lib
-from .collision import Collider
+from .collision import MORTON_BITS, Collider
 
 
 def shard_range(n, world, rank):
@@ -181,7 +181,7 @@ class ShardedCollider:
     WINDOW = 256      # sorted leaves per window of the build (csrc/refit.cu: BR_WINDOW)
 
     def __init__(self, ctx, size, ngroups, group_size, coord_dtype=dtype('float32'), group=None, src=0,
-                 mode="broadcast_tree", balance=False, query_weight=1, graph=False):
+                 mode="broadcast_tree", balance=False, query_weight=1, graph=False, sharded_sort=True):
         """mode "broadcast_tree" (north_star): rank `src` sorts, builds and refits; the
         traversal data (68 B per sphere) is broadcast.
         mode "replicate_build": the INPUT (coords + radii, 20 B per sphere) is broadcast
@@ -198,7 +198,10 @@ class ShardedCollider:
         of other ranks' windows are then fetched ON DEMAND -- only the subtrees the rank's own queries can
         enter -- straight from the owners' HBM over NVLink (peer loads from buffers mapped with CUDA IPC,
         `collision_b200.shared`).  Query ranges = the window ranges (no `balance`).  Constructing the object
-        is collective (the shared buffers are exchanged).
+        is collective (the shared buffers are exchanged).  With sharded_sort=True (default) the SORT is dealt
+        out too: every rank still holds all the codes, but sorts only the buckets of the top digit that cover
+        its own windows (`col_shard_sort`: count, select, collect, sort -- bit-identical positions), the codes
+        the spanning nodes need travel with the handed-over roots and the ids of fetched leaves with the halo.
         balance=True: after every call (with sync_totals) that WRITES rows the query ranges of
         the next call are re-cut from the all-gathered row totals (cost of a range = rows +
         query_weight * queries, accumulated in a `DensityModel`), so that a clustered scene
@@ -233,6 +236,7 @@ class ShardedCollider:
         self._graphs = {}
         self._graph_candidate = None
         self.graph_replays = 0
+        self.sharded_sort = bool(sharded_sort) and mode == "sharded_build"
         if mode == "sharded_build":
             if balance:
                 raise ValueError("mode 'sharded_build' splits the queries where it splits the windows: no balance")
@@ -252,6 +256,13 @@ class ShardedCollider:
         self._sb_wide = SharedBuffer(ctx, c._wide_buf.numel(), self.group)
         self._sb_bounds = SharedBuffer(ctx, c._bounds_buf.numel(), self.group)
         c._wide_buf, c._bounds_buf = self._sb_wide.local, self._sb_bounds.local
+        self._sb_ids = None
+        if self.sharded_sort:
+            # the sorted ids, too: a fetched leaf's id is the owner's to give
+            self._sb_ids = SharedBuffer(ctx, c._ids_bufs[1].numel(), self.group)
+            c._ids_bufs[1] = self._sb_ids.local
+            self._shard_sort_scratch = _lib.alloc_bytes(ctx, L.col_shard_sort_scratch_bytes(n))
+            self._sort_range = torch.zeros(4, dtype=torch.int32, device=ctx)   # {offset, count, first, last bucket}
         most = max(e - b for b, e in zip(self.edges, self.edges[1:]))
         self._cap = max(1024, most // 16)                    # subtree roots a rank may hand over (typically 1.6 % of its leaves)
         self._list_cap = max(4096, n // 16)                  # remote subtrees a rank may ask for
@@ -285,6 +296,10 @@ class ShardedCollider:
             self._sb_wide.close()
             self._sb_bounds.close()
             self._sb_wide = self._sb_bounds = None
+            if self._sb_ids is not None:
+                c._ids_bufs[1] = None
+                self._sb_ids.close()
+                self._sb_ids = None
 
     def suggested_capacity(self, headroom=1.5):
         """Rows to make room for on this rank after a count-only call: with balance=True the
@@ -397,8 +412,9 @@ class ShardedCollider:
             _lib.check(L.col_morton(P(c._codes_bufs[0]) + 4 * b, None, P(coords_buf) + b * 4 * isz, P(c._scene_buf),
                                     code, e - b, e - b, S), "col_morton")
         gather_slices(c._codes_bufs[0][:4 * n], 4, n, self.group)
-        _lib.check(L.col_range(P(c._ids_bufs[0]), n, S), "col_range")
-        c._mark(cq, "morton", 2)
+        if not self.sharded_sort:
+            _lib.check(L.col_range(P(c._ids_bufs[0]), n, S), "col_range")
+        c._mark(cq, "morton", 1 if self.sharded_sort else 2)
         # the scene itself travels on the side stream, behind the codes in NCCL's order
         ready = torch.cuda.Event()
         ready.record(cq)
@@ -408,7 +424,16 @@ class ShardedCollider:
             gather_slices(radii_buf, isz, n, self.group)
             gathered = torch.cuda.Event()
             gathered.record(self._side)
-        c._sort_codes(cq)
+        if self.sharded_sort:
+            # own windows plus one position either side (the window pass reads its neighbours' codes)
+            lo, hi = max(self.q_begin, 1) - 1, min(self.q_end, n - 1)
+            if self.q_end > self.q_begin:
+                _lib.check(L.col_shard_sort(P(c._codes_bufs[0]), n, lo, hi, MORTON_BITS, P(c._codes_bufs[1]),
+                                            P(c._ids_bufs[1]), P(self._sort_range), P(self._shard_sort_scratch), S),
+                           "col_shard_sort")
+            c._mark(cq, "sort", 5 + (MORTON_BITS + 7) // 8 + 2)   # count, bases, select, collect; histogram, bases, passes
+        else:
+            c._sort_codes(cq)
         cq.wait_event(gathered)
         c._mark(cq, "broadcast", 0)      # (what is left of the scene's all-gather after the sort)
 
@@ -432,7 +457,9 @@ class ShardedCollider:
         _lib.check(L.col_shard_halo(P(self._gathered), self._cap, self.world, self.rank, P(c._wide_buf),
                                     P(c._bounds_buf), P(c._scene_buf), code, P(c._flags_buf), P(self._list),
                                     self._list_cap, P(self._sb_wide.table), P(self._sb_bounds.table),
-                                    P(self._win_edges_dev), n, self.q_begin, self.q_end, S), "col_shard_halo")
+                                    P(self._win_edges_dev), n, self.q_begin, self.q_end,
+                                    P(self._sb_ids.table) if self.sharded_sort else None,
+                                    P(c._ids_bufs[1]) if self.sharded_sort else None, S), "col_shard_halo")
         c._mark(cq, "halo", 2)
 
     def _enqueue(self, cq, coords_buf, radii_buf, n_collisions_buf, collisions_buf, n_collisions):

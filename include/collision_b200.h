@@ -319,7 +319,20 @@ int col_ipc_close(void* ptr);
  *                            win_edges: world + 1 window indices (device), rank r owns [win_edges[r], win_edges[r+1]);
  *                            list: col_shard_list_bytes(list_cap) bytes of scratch.  After it the traversal of
  *                            the rank's own queries [leaf_begin, leaf_end) finds everything it touches locally.
- * Overflow of `cap` / `list_cap` sets word 1 of the respective header (the host checks it when it next syncs). */
+ *                            ids_table / ids_sorted (may both be NULL): the sphere ids of the fetched leaves are
+ *                            copied from the owners as well (needed after col_shard_sort, see below).
+ * Overflow of `cap` / `list_cap` sets word 1 of the respective header (the host checks it when it next syncs).
+ *
+ * col_shard_sort           = the SORT dealt out the same way: positions [pos_lo, pos_hi] of the stable sort of all
+ *                            n codes (ids = input positions), written at codes_sorted / ids_sorted + those positions
+ *                            and nowhere else -- bit-identical to what col_sort_pairs writes there.  The codes' top
+ *                            8-bit digit is counted, the buckets covering the positions are selected ON THE DEVICE
+ *                            (range_out: 4 words {offset, count, first bucket, last bucket}; no host round trip),
+ *                            their (code, index) pairs are collected in input order and sorted on end_bit bits.
+ *                            `codes` must be 16-byte aligned; scratch: col_shard_sort_scratch_bytes(n).
+ *                            The records a rank hands over carry the codes at their ends, and col_shard_top writes
+ *                            those of the other ranks into codes_sorted (all the top pass reads), so a rank never
+ *                            needs the rest of the sorted order. */
 size_t col_shard_packed_bytes(uint32_t cap, int dtype);
 size_t col_shard_list_bytes(uint32_t list_cap);
 int col_shard_build_windows(const uint32_t* codes_sorted, const uint32_t* ids_sorted, void* nodes, void* wide,
@@ -327,12 +340,17 @@ int col_shard_build_windows(const uint32_t* codes_sorted, const uint32_t* ids_so
                             const void* scene2x4, int dtype, uint32_t n, uint32_t win_begin, uint32_t win_end,
                             void* packed, uint32_t cap, void* stream);
 int col_shard_top(const void* gathered, uint32_t cap, uint32_t world, uint32_t my_rank,
-                  const uint32_t* codes_sorted, void* nodes, void* wide, uint32_t* flags, void* bounds,
+                  uint32_t* codes_sorted, void* nodes, void* wide, uint32_t* flags, void* bounds,
                   const void* scene2x4, int dtype, uint32_t n, void* stream);
 int col_shard_halo(const void* gathered, uint32_t cap, uint32_t world, uint32_t my_rank, void* wide, void* bounds,
                    const void* scene2x4, int dtype, uint32_t* flags, void* list, uint32_t list_cap,
                    const uint64_t* wide_table, const uint64_t* bounds_table, const uint32_t* win_edges,
-                   uint32_t n, uint32_t leaf_begin, uint32_t leaf_end, void* stream);
+                   uint32_t n, uint32_t leaf_begin, uint32_t leaf_end, const uint64_t* ids_table,
+                   uint32_t* ids_sorted, void* stream);
+size_t col_shard_sort_scratch_bytes(uint64_t n);
+int col_shard_sort(const uint32_t* codes, uint32_t n, uint32_t pos_lo, uint32_t pos_hi, uint32_t end_bit,
+                   uint32_t* codes_sorted, uint32_t* ids_sorted, uint32_t* range_out, void* scratch,
+                   void* stream);
 
 /* utility: u32 fill (cl.enqueue_fill_buffer sites, e.g. collision/offset.py:43) */
 int col_fill_u32(uint32_t* dst, uint32_t value, uint64_t n, void* stream);

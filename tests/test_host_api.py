@@ -30,7 +30,7 @@ def test_library_exports_every_header_symbol():
     # the ctypes table binds exactly the header's surface
     assert sorted(_lib.SIGNATURES) == names
     L = _lib.lib()
-    assert L.col_abi_version() == 1 and L.col_built_arch() == 100
+    assert L.col_abi_version() == 2 and L.col_built_arch() == 100
 
 
 def test_scratch_queries_are_pure_host():

@@ -13,7 +13,8 @@ import golden_data as G
 
 pytestmark = pytest.mark.gpu
 
-MODES = ("broadcast_tree", "replicate_build", "gather_inputs", "sharded_build")
+# "sharded_build" alone = with the sort dealt out as well (the default); "/replicated_sort" = every rank sorts everything
+MODES = ("broadcast_tree", "replicate_build", "gather_inputs", "sharded_build", "sharded_build/replicated_sort")
 
 
 def _free_port():
@@ -41,6 +42,7 @@ def _worker(rank, world, port, n, kind, mode, balance, graph, frames, raw, tmpdi
     dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
     try:
         from collision_b200.sharded import ShardedCollider, shard_range
+        mode, _, variant = mode.partition("/")
         c, r = _scene(n, kind)
         b, e = shard_range(n, world, rank)
         cq = torch.cuda.Stream(dev)
@@ -60,7 +62,9 @@ def _worker(rank, world, port, n, kind, mode, balance, graph, frames, raw, tmpdi
                 ct, rt = ct.view(torch.uint8).reshape(-1), rt.view(torch.uint8).reshape(-1)
             return ct, rt
 
-        col = ShardedCollider(dev, n, 8, 64, mode=mode, balance=balance, graph=graph)
+        col = ShardedCollider(dev, n, 8, 64, mode=mode, balance=balance, graph=graph,
+                              sharded_sort=variant != "replicated_sort")
+        assert col.sharded_sort == (mode == "sharded_build" and not variant)
         n_buf = torch.zeros(1, dtype=torch.int32, device=dev)
         ct, rt = inputs()
         torch.cuda.synchronize()
@@ -104,7 +108,7 @@ def _run(tmp_path, oracle, n, kind, mode, balance=False, graph=False, frames=1, 
     if not torch.cuda.is_available() or torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
     from collision_b200.sharded import ShardedCollider
-    if mode not in ShardedCollider.MODES:
+    if mode.partition("/")[0] not in ShardedCollider.MODES:
         pytest.skip("mode {} not built".format(mode))
     world = 2
     mp.spawn(_worker, args=(world, _free_port(), n, kind, mode, balance, graph, frames, raw, str(tmp_path)),
@@ -125,6 +129,12 @@ def _run(tmp_path, oracle, n, kind, mode, balance=False, graph=False, frames=1, 
 @pytest.mark.parametrize("n,kind", [(20011, "uniform"), (16384, "duplicates")])
 def test_two_ranks_equal_single_rank(tmp_path, oracle, mode, n, kind):
     _run(tmp_path, oracle, n, kind, mode)
+
+
+@pytest.mark.parametrize("mode", ["sharded_build", "sharded_build/replicated_sort"])
+def test_two_ranks_many_windows(tmp_path, oracle, mode):
+    """Enough spheres for many windows, several tiles of the collect pass and unequal buckets per rank."""
+    _run(tmp_path, oracle, 300007, "skewed", mode)
 
 
 @pytest.mark.parametrize("mode", ["gather_inputs", "sharded_build"])
