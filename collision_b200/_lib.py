@@ -72,6 +72,12 @@ SIGNATURES = {
                               _vp, _vp, _vp]),
     "col_shard_sort_scratch_bytes": (_sz, [_u64]),
     "col_shard_sort": (_int, [_vp, _u32, _u32, _u32, _u32, _vp, _vp, _vp, _vp, _vp]),
+    "col_shard_count": (_int, [_vp, _u32, _u32, _vp, _vp]),
+    "col_shard_push_scratch_bytes": (_sz, [_u64, _u32]),
+    "col_shard_push": (_int, [_vp, _u32, _u32, _vp, _u32, _vp, _u32, _u32, _vp, _vp, _int, _u32, _vp, _vp, _vp, _vp, _vp,
+                              _vp, _vp]),
+    "col_shard_sort_received_scratch_bytes": (_sz, [_u64]),
+    "col_shard_sort_received": (_int, [_vp, _vp, _u32, _vp, _u32, _vp, _vp, _vp, _vp, _vp]),
     "col_fill_u32": (_int, [_vp, _u32, _u64, _vp]),
     "col_range": (_int, [_vp, _u64, _vp]),
     "col_copy": (_int, [_vp, _vp, _u64, _vp]),

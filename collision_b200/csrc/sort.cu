@@ -718,3 +718,315 @@ COL_API int col_shard_sort(const uint32_t* codes, uint32_t n, uint32_t pos_lo, u
     return run_passes<uint32_t>(keys, codes_sorted, vals, ids_sorted, n, 0, RADIX_BITS, npass, scratch + L.sort, SL, s,
                                 range_out);
 }
+
+// ================================================================ sharded sort, exchanged (multi-GPU)
+// The same selection as col_shard_sort, but without ANY rank ever holding all the codes or the whole
+// scene: the spheres a rank's windows need are PUSHED to it by their holders, straight into its HBM
+// over NVLink (peer stores into buffers mapped with CUDA IPC), compacted on the way.
+//   col_shard_count   : top-digit counts of the rank's OWN slice of the codes (256 words; the caller
+//                       all-gathers them: 1 KB per rank instead of 4 B per sphere);
+//   col_shard_push    : from the gathered counts every rank derives the same plan -- bucket starts, and for
+//                       every rank r the buckets covering its positions -- plus where ITS contribution
+//                       to r's receive buffers starts (the spheres of lower ranks' slices in those buckets
+//                       come first: input order).  Then one stable compaction of the own slice per
+//                       destination, writing {code, sphere id, coordinates, radius} to the destination;
+//   (the caller runs a collective here: all pushes have landed once every rank has passed it)
+//   col_shard_sort_received : stable sort of the received codes (value = place in the receive buffers),
+//                       placed at the rank's positions of the global order; ids_sorted = the received
+//                       ids in that order.  The build reads coordinates and radii through the sorted
+//                       places, from the receive buffers.
+// The received list is in input order (rank-major, then slice order), exactly what col_shard_sort's
+// collect pass produces from all the codes: positions come out bit-identical to the full sort.
+namespace {
+
+constexpr uint32_t PLAN_WORDS = 8;    // per destination: {offset, count, first bucket, last bucket, my base, -, -, -}
+constexpr uint32_t NO_BUCKET = 0x100; // first = last = NO_BUCKET: the destination takes nothing
+
+// hist_all: world x 256 counts (rank-major); pos: world x {pos_lo, pos_hi} (pos_lo > pos_hi: nothing)
+__global__ void __launch_bounds__(RADIX) plan_kernel(const uint32_t* __restrict__ hist_all, uint32_t world, uint32_t me,
+                                                     const uint32_t* __restrict__ pos, uint32_t n,
+                                                     uint32_t* __restrict__ plan) {
+    __shared__ uint32_t s_start[RADIX + 1];
+    __shared__ uint32_t s_warp[RADIX / 32];
+    __shared__ uint32_t s_lo, s_hi, s_base;
+    const uint32_t d = threadIdx.x;
+    uint32_t total = 0, before_me = 0;
+    for (uint32_t r = 0; r < world; r++) {
+        const uint32_t c = hist_all[r * RADIX + d];
+        total += c;
+        if (r < me) before_me += c;
+    }
+    uint32_t inc = total;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t up = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane_id() >= o) inc += up;
+    }
+    if (lane_id() == 31) s_warp[d >> 5] = inc;
+    __syncthreads();
+    uint32_t base = 0;
+    for (uint32_t w = 0; w < (d >> 5); w++) base += s_warp[w];
+    s_start[d] = base + inc - total;
+    if (d == RADIX - 1) s_start[RADIX] = base + inc;   // = n
+    __syncthreads();
+    for (uint32_t r = 0; r < world; r++) {
+        const uint32_t pos_lo = pos[2 * r], pos_hi = min(pos[2 * r + 1], n - 1);
+        if (d == 0) { s_lo = 0; s_hi = 0; s_base = 0; }
+        __syncthreads();
+        const bool any = pos_lo <= pos_hi && pos_lo < n;
+        if (any) {
+            if (s_start[d] <= pos_lo) atomicMax(&s_lo, d);
+            if (s_start[d] <= pos_hi) atomicMax(&s_hi, d);
+        }
+        __syncthreads();
+        if (any && d >= s_lo && d <= s_hi && before_me) atomicAdd(&s_base, before_me);
+        __syncthreads();
+        if (d == 0) {
+            uint32_t* p = plan + r * PLAN_WORDS;
+            p[0] = any ? s_start[s_lo] : 0u;
+            p[1] = any ? s_start[s_hi + 1] - s_start[s_lo] : 0u;
+            p[2] = any ? s_lo : NO_BUCKET;
+            p[3] = any ? s_hi : NO_BUCKET;
+            p[4] = s_base;
+            p[5] = p[6] = p[7] = 0u;
+        }
+        __syncthreads();
+    }
+}
+
+// collect_kernel with the scene riding along and the output somewhere else: entries go to
+// dst_* + plan[4] + (their rank among the collected entries of this slice).  W = words per scalar.
+template <int W>
+__global__ void __launch_bounds__(COLLECT_THREADS)
+collect_push_kernel(const uint32_t* __restrict__ codes, uint32_t n, uint32_t id_base, uint32_t shift, uint32_t mask,
+                    const uint32_t* __restrict__ plan, const uint4* __restrict__ coords, const uint32_t* __restrict__ radii,
+                    uint32_t* __restrict__ dst_codes, uint32_t* __restrict__ dst_ids, uint4* __restrict__ dst_coords,
+                    uint32_t* __restrict__ dst_radii, unsigned* ticket, uint64_t* status) {
+    __shared__ unsigned s_tile;
+    __shared__ uint32_t s_warp_total[COLLECT_THREADS / 32];
+    __shared__ uint32_t s_tile_prefix;
+    if (threadIdx.x == 0) s_tile = atomicAdd(ticket, 1u);
+    __syncthreads();
+    const unsigned tile = s_tile;
+    const uint32_t tile_base = tile * (uint32_t)COLLECT_TILE;
+    const unsigned warp = threadIdx.x >> 5, lane = lane_id();
+    const uint32_t warp_base = tile_base + warp * COLLECT_WARP_ITEMS;
+    const bool full = (uint64_t)tile_base + COLLECT_TILE <= n;
+    const uint32_t d_lo = plan[2], span = plan[3] - d_lo, out0 = plan[4];
+
+    uint4 v[COLLECT_VECS];
+    uint32_t sel[COLLECT_VECS], excl[COLLECT_VECS];
+    uint32_t row_base = 0;
+#pragma unroll
+    for (int k = 0; k < COLLECT_VECS; k++) {
+        const uint32_t e = warp_base + (uint32_t)(k * 32 + lane) * 4;
+        if (full) {
+            v[k] = *reinterpret_cast<const uint4*>(codes + e);
+        } else {
+            v[k].x = e + 0 < n ? codes[e + 0] : 0u;
+            v[k].y = e + 1 < n ? codes[e + 1] : 0u;
+            v[k].z = e + 2 < n ? codes[e + 2] : 0u;
+            v[k].w = e + 3 < n ? codes[e + 3] : 0u;
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < COLLECT_VECS; k++) {
+        const uint32_t e = warp_base + (uint32_t)(k * 32 + lane) * 4;
+        uint32_t m = 0;
+        m |= ((((v[k].x >> shift) & mask) - d_lo) <= span && (full || e + 0 < n)) ? 1u : 0u;
+        m |= ((((v[k].y >> shift) & mask) - d_lo) <= span && (full || e + 1 < n)) ? 2u : 0u;
+        m |= ((((v[k].z >> shift) & mask) - d_lo) <= span && (full || e + 2 < n)) ? 4u : 0u;
+        m |= ((((v[k].w >> shift) & mask) - d_lo) <= span && (full || e + 3 < n)) ? 8u : 0u;
+        sel[k] = m;
+        const uint32_t c = (uint32_t)__popc(m);
+        uint32_t inc = c;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t up = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += up;
+        }
+        excl[k] = row_base + inc - c;
+        row_base += __shfl_sync(0xffffffffu, inc, 31);
+    }
+    if (lane == 0) s_warp_total[warp] = row_base;
+    __syncthreads();
+    uint32_t warp_prefix = 0, tile_total = 0;
+#pragma unroll
+    for (int w = 0; w < COLLECT_THREADS / 32; w++) {
+        const uint32_t t = s_warp_total[w];
+        if (w < (int)warp) warp_prefix += t;
+        tile_total += t;
+    }
+    if (warp == 0) {
+        constexpr uint64_t PARTIAL = 1ull << 62, INCLUSIVE = 2ull << 62, VALUE = (1ull << 62) - 1;
+        uint64_t prefix = 0;
+        if (tile == 0) {
+            if (lane == 0) st_relaxed_u64(status, INCLUSIVE | tile_total);
+        } else {
+            if (lane == 0) st_relaxed_u64(status + tile, PARTIAL | tile_total);
+            int64_t look = (int64_t)tile - 1 - lane;
+            while (true) {
+                uint64_t st = INCLUSIVE;
+                if (look >= 0) {
+                    do { st = ld_relaxed_u64(status + look); } while ((st >> 62) == 0);
+                }
+                const unsigned inc_mask = __ballot_sync(0xffffffffu, (st >> 62) == 2);
+                const unsigned first = inc_mask ? (unsigned)__ffs(inc_mask) - 1 : 31u;
+                uint64_t c = (lane <= first) ? (st & VALUE) : 0;
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+                prefix += c;
+                if (inc_mask) break;
+                look -= 32;
+            }
+            if (lane == 0) st_relaxed_u64(status + tile, INCLUSIVE | (prefix + tile_total));
+        }
+        if (lane == 0) s_tile_prefix = (uint32_t)prefix;
+    }
+    __syncthreads();
+    const uint32_t base = out0 + s_tile_prefix + warp_prefix;
+#pragma unroll
+    for (int k = 0; k < COLLECT_VECS; k++) {
+        const uint32_t e = warp_base + (uint32_t)(k * 32 + lane) * 4;
+        uint32_t dst = base + excl[k];
+        const uint32_t m = sel[k];
+        const uint32_t cv[4] = {v[k].x, v[k].y, v[k].z, v[k].w};
+#pragma unroll
+        for (int h = 0; h < 4; h++) {
+            if (m & (1u << h)) {
+                const uint32_t src = e + h;
+#ifdef COL_DEBUG
+                if (dst >= plan[1]) __trap();   // more than the destination's buckets hold
+#endif
+                dst_codes[dst] = cv[h];
+                dst_ids[dst] = id_base + src;
+#pragma unroll
+                for (int w = 0; w < W; w++) {
+                    dst_coords[(size_t)dst * W + w] = ld_stream_u4(coords + (size_t)src * W + w);
+                    dst_radii[(size_t)dst * W + w] = ld_stream_u32(radii + (size_t)src * W + w);
+                }
+                dst++;
+            }
+        }
+    }
+}
+
+__global__ void __launch_bounds__(256) iota_range_kernel(uint32_t* p, const uint32_t* __restrict__ range) {
+    const uint32_t n = range[1];
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) p[i] = i;
+}
+
+// ids_sorted[offset + i] = recv_ids[place_sorted[offset + i]]
+__global__ void __launch_bounds__(256) gather_ids_range_kernel(uint32_t* __restrict__ ids_sorted,
+                                                               const uint32_t* __restrict__ place_sorted,
+                                                               const uint32_t* __restrict__ recv_ids,
+                                                               const uint32_t* __restrict__ range) {
+    const uint32_t off = range[0], n = range[1];
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+        ids_sorted[off + i] = __ldg(recv_ids + place_sorted[off + i]);
+}
+
+struct PushLayout {
+    size_t tickets, status, status_stride, total;
+    uint64_t tiles;
+};
+
+PushLayout push_layout(uint64_t n_own, uint32_t world) {
+    PushLayout L;
+    L.tiles = (n_own + COLLECT_TILE - 1) / COLLECT_TILE;
+    if (L.tiles == 0) L.tiles = 1;
+    size_t off = 0;
+    L.tickets = off; off += align_up(sizeof(uint32_t) * world);
+    L.status = off;
+    L.status_stride = align_up(sizeof(uint64_t) * L.tiles);
+    off += L.status_stride * world;
+    L.total = off;
+    return L;
+}
+
+}  // namespace
+
+COL_API int col_shard_count(const uint32_t* codes_own, uint32_t n_own, uint32_t end_bit, uint32_t* hist256, void* stream) {
+    if (!hist256 || (n_own && !codes_own)) return COL_ERR_BAD_ARG;
+    if (end_bit == 0 || end_bit > 32) end_bit = 32;
+    cudaStream_t s = col_stream(stream);
+    COL_CUDA(cudaMemsetAsync(hist256, 0, sizeof(uint32_t) * RADIX, s));
+    if (n_own == 0) return 0;
+    const uint32_t top_shift = end_bit > RADIX_BITS ? end_bit - RADIX_BITS : 0;
+    const uint32_t top_bits = end_bit > RADIX_BITS ? RADIX_BITS : end_bit;
+    const uint64_t want = ((uint64_t)n_own + HIST_THREADS * HIST_ITEMS - 1) / (HIST_THREADS * HIST_ITEMS);
+    const unsigned blocks = (unsigned)(want > COL_NUM_SMS * 4 ? COL_NUM_SMS * 4 : want);
+    histogram_kernel<uint32_t><<<blocks, HIST_THREADS, 0, s>>>(codes_own, n_own, hist256, top_shift, top_bits, 1, nullptr);
+    COL_CHECK_LAUNCH();
+    return 0;
+}
+
+COL_API size_t col_shard_push_scratch_bytes(uint64_t n_own, uint32_t world) { return push_layout(n_own, world).total; }
+
+COL_API int col_shard_push(const uint32_t* hist_all, uint32_t world, uint32_t my_rank, const uint32_t* pos_table,
+                           uint32_t n, const uint32_t* codes_own, uint32_t n_own, uint32_t id_base,
+                           const void* coords_own, const void* radii_own, int dtype, uint32_t end_bit,
+                           const uint64_t* h_recv_codes, const uint64_t* h_recv_ids, const uint64_t* h_recv_coords,
+                           const uint64_t* h_recv_radii, uint32_t* plan, void* scratch_v, void* stream) {
+    if (!hist_all || !pos_table || !plan || !scratch_v || !h_recv_codes || !h_recv_ids || !h_recv_coords || !h_recv_radii ||
+        world == 0 || my_rank >= world || n == 0)
+        return COL_ERR_BAD_ARG;
+    if (n_own && (!codes_own || !coords_own || !radii_own)) return COL_ERR_BAD_ARG;
+    if (dtype != COL_F32 && dtype != COL_F64) return COL_ERR_UNSUPPORTED;
+    if (n > (1u << 30)) return COL_ERR_TOO_LARGE;
+    if ((reinterpret_cast<uintptr_t>(codes_own) & 15u) != 0 || (reinterpret_cast<uintptr_t>(coords_own) & 15u) != 0)
+        return COL_ERR_BAD_ARG;
+    if (end_bit == 0 || end_bit > 32) end_bit = 32;
+    cudaStream_t s = col_stream(stream);
+    char* scratch = reinterpret_cast<char*>(scratch_v);
+    const PushLayout L = push_layout(n_own, world);
+    const uint32_t top_shift = end_bit > RADIX_BITS ? end_bit - RADIX_BITS : 0;
+    const uint32_t top_bits = end_bit > RADIX_BITS ? RADIX_BITS : end_bit;
+    plan_kernel<<<1, RADIX, 0, s>>>(hist_all, world, my_rank, pos_table, n, plan);
+    COL_CHECK_LAUNCH();
+    if (n_own == 0) return 0;
+    COL_CUDA(cudaMemsetAsync(scratch, 0, L.total, s));
+    for (uint32_t k = 0; k < world; k++) {
+        const uint32_t r = (my_rank + k) % world;   // every rank starts with its own buffers, then round the ring
+        unsigned* ticket = reinterpret_cast<unsigned*>(scratch + L.tickets) + r;
+        uint64_t* status = reinterpret_cast<uint64_t*>(scratch + L.status + L.status_stride * r);
+        if (dtype == COL_F32)
+            collect_push_kernel<1><<<(unsigned)L.tiles, COLLECT_THREADS, 0, s>>>(
+                codes_own, n_own, id_base, top_shift, (1u << top_bits) - 1, plan + r * PLAN_WORDS, (const uint4*)coords_own,
+                (const uint32_t*)radii_own, (uint32_t*)h_recv_codes[r], (uint32_t*)h_recv_ids[r], (uint4*)h_recv_coords[r],
+                (uint32_t*)h_recv_radii[r], ticket, status);
+        else
+            collect_push_kernel<2><<<(unsigned)L.tiles, COLLECT_THREADS, 0, s>>>(
+                codes_own, n_own, id_base, top_shift, (1u << top_bits) - 1, plan + r * PLAN_WORDS, (const uint4*)coords_own,
+                (const uint32_t*)radii_own, (uint32_t*)h_recv_codes[r], (uint32_t*)h_recv_ids[r], (uint4*)h_recv_coords[r],
+                (uint32_t*)h_recv_radii[r], ticket, status);
+        COL_CHECK_LAUNCH();
+    }
+    return 0;
+}
+
+COL_API size_t col_shard_sort_received_scratch_bytes(uint64_t n) {
+    return align_up((size_t)n * 4) + sort_layout(n, 4, 4).total;
+}
+
+COL_API int col_shard_sort_received(uint32_t* recv_codes, const uint32_t* recv_ids, uint32_t n, const uint32_t* range,
+                                    uint32_t end_bit, uint32_t* codes_sorted, uint32_t* place_sorted, uint32_t* ids_sorted,
+                                    void* scratch_v, void* stream) {
+    if (!recv_codes || !recv_ids || !range || !codes_sorted || !place_sorted || !ids_sorted || !scratch_v || n == 0)
+        return COL_ERR_BAD_ARG;
+    if (n > (1u << 30)) return COL_ERR_TOO_LARGE;
+    if (end_bit == 0 || end_bit > 32) end_bit = 32;
+    cudaStream_t s = col_stream(stream);
+    char* scratch = reinterpret_cast<char*>(scratch_v);
+    uint32_t* places = reinterpret_cast<uint32_t*>(scratch);
+    iota_range_kernel<<<COL_NUM_SMS * 8, 256, 0, s>>>(places, range);
+    COL_CHECK_LAUNCH();
+    const uint32_t npass = (end_bit + RADIX_BITS - 1) / RADIX_BITS;
+    const SortLayout SL = sort_layout(n, 4, 4);
+    const int rc = run_passes<uint32_t>(recv_codes, codes_sorted, places, place_sorted, n, 0, RADIX_BITS, npass,
+                                        scratch + align_up((size_t)n * 4), SL, s, range);
+    if (rc) return rc;
+    gather_ids_range_kernel<<<COL_NUM_SMS * 8, 256, 0, s>>>(ids_sorted, place_sorted, recv_ids, range);
+    COL_CHECK_LAUNCH();
+    return 0;
+}

@@ -198,10 +198,18 @@ class ShardedCollider:
         of other ranks' windows are then fetched ON DEMAND -- only the subtrees the rank's own queries can
         enter -- straight from the owners' HBM over NVLink (peer loads from buffers mapped with CUDA IPC,
         `collision_b200.shared`).  Query ranges = the window ranges (no `balance`).  Constructing the object
-        is collective (the shared buffers are exchanged).  With sharded_sort=True (default) the SORT is dealt
-        out too: every rank still holds all the codes, but sorts only the buckets of the top digit that cover
-        its own windows (`col_shard_sort`: count, select, collect, sort -- bit-identical positions), the codes
-        the spanning nodes need travel with the handed-over roots and the ids of fetched leaves with the halo.
+        is collective (the shared buffers are exchanged).  The SORT is dealt out too (sharded_sort):
+          True / "exchange" (default): no rank ever holds all the codes or the whole scene.  The top 8-bit digit
+            of the rank's own codes is counted, the counts (1 KB) are all-gathered, every rank derives the same
+            plan -- which buckets cover which rank's windows -- and PUSHES the {code, id, coordinates, radius}
+            of its own spheres in those buckets straight into the receiving rank's HBM (peer stores over
+            NVLink, compacted in input order: csrc/sort.cu col_shard_push); a rank then sorts what it received.
+            28 bytes per sphere cross NVLink once, instead of all-gathers of 4 + 20 bytes per sphere TO EVERY RANK.
+          "local": every rank still gathers all the codes and the scene, but sorts only the buckets covering
+            its own windows (`col_shard_sort`: count, select, collect, sort).
+          False / "replicated": every rank sorts everything.
+        The sorted positions are bit-identical in all three; the codes the spanning nodes need travel with the
+        handed-over roots and the ids of fetched leaves with the halo.
         balance=True: after every call (with sync_totals) that WRITES rows the query ranges of
         the next call are re-cut from the all-gathered row totals (cost of a range = rows +
         query_weight * queries, accumulated in a `DensityModel`), so that a clustered scene
@@ -236,7 +244,11 @@ class ShardedCollider:
         self._graphs = {}
         self._graph_candidate = None
         self.graph_replays = 0
-        self.sharded_sort = bool(sharded_sort) and mode == "sharded_build"
+        sort_mode = {True: "exchange", False: "replicated", None: "replicated"}.get(sharded_sort, sharded_sort)
+        if sort_mode not in ("exchange", "local", "replicated"):
+            raise ValueError("sharded_sort must be True / 'exchange', 'local' or False / 'replicated'")
+        self.sort_mode = sort_mode if mode == "sharded_build" else "replicated"
+        self.sharded_sort = self.sort_mode != "replicated"
         if mode == "sharded_build":
             if balance:
                 raise ValueError("mode 'sharded_build' splits the queries where it splits the windows: no balance")
@@ -261,8 +273,27 @@ class ShardedCollider:
             # the sorted ids, too: a fetched leaf's id is the owner's to give
             self._sb_ids = SharedBuffer(ctx, c._ids_bufs[1].numel(), self.group)
             c._ids_bufs[1] = self._sb_ids.local
+        self._sb_recv = []
+        if self.sort_mode == "local":
             self._shard_sort_scratch = _lib.alloc_bytes(ctx, L.col_shard_sort_scratch_bytes(n))
             self._sort_range = torch.zeros(4, dtype=torch.int32, device=ctx)   # {offset, count, first, last bucket}
+        if self.sort_mode == "exchange":
+            import ctypes as C
+            b, e = shard_range(n, k, self.rank)
+            # receive buffers (codes, ids, coordinates, radii), each sized for the worst case: one bucket holds
+            # the whole scene and every rank receives all of it
+            self._sb_recv = [SharedBuffer(ctx, n * w, self.group) for w in (4, 4, 4 * isz, isz)]
+            self._recv_tables = [(C.c_uint64 * k)(*sb.peer_ptrs) for sb in self._sb_recv]
+            self._hist_own = torch.zeros(256, dtype=torch.int32, device=ctx)
+            self._hist_all = torch.zeros(256 * k, dtype=torch.int32, device=ctx)
+            self._plan = torch.zeros(8 * k, dtype=torch.int32, device=ctx)
+            pos = []
+            for qb, qe in zip(self.edges, self.edges[1:]):      # own windows plus one position either side
+                pos += [max(qb, 1) - 1, min(qe, n - 1)] if qe > qb else [1, 0]
+            self._pos_table = torch.tensor(pos, dtype=torch.int32, device=ctx)
+            self._push_scratch = _lib.alloc_bytes(ctx, L.col_shard_push_scratch_bytes(e - b, k))
+            self._recv_sort_scratch = _lib.alloc_bytes(ctx, L.col_shard_sort_received_scratch_bytes(n))
+            self._token = torch.zeros(1, dtype=torch.int32, device=ctx)
         most = max(e - b for b, e in zip(self.edges, self.edges[1:]))
         self._cap = max(1024, most // 16)                    # subtree roots a rank may hand over (typically 1.6 % of its leaves)
         self._list_cap = max(4096, n // 16)                  # remote subtrees a rank may ask for
@@ -300,6 +331,9 @@ class ShardedCollider:
                 c._ids_bufs[1] = None
                 self._sb_ids.close()
                 self._sb_ids = None
+            for sb in self._sb_recv:
+                sb.close()
+            self._sb_recv = []
 
     def suggested_capacity(self, headroom=1.5):
         """Rows to make room for on this rank after a count-only call: with balance=True the
@@ -408,11 +442,13 @@ class ShardedCollider:
         dist.all_reduce(scene, op=dist.ReduceOp.MIN, group=self.group)
         scene[4:].neg_()
         c._mark(cq, "bounds", 1)
+        if self.sort_mode == "exchange":
+            return self._front_exchange(cq, coords_buf, radii_buf, b, e)
         if e > b:
             _lib.check(L.col_morton(P(c._codes_bufs[0]) + 4 * b, None, P(coords_buf) + b * 4 * isz, P(c._scene_buf),
                                     code, e - b, e - b, S), "col_morton")
         gather_slices(c._codes_bufs[0][:4 * n], 4, n, self.group)
-        if not self.sharded_sort:
+        if self.sort_mode == "replicated":
             _lib.check(L.col_range(P(c._ids_bufs[0]), n, S), "col_range")
         c._mark(cq, "morton", 1 if self.sharded_sort else 2)
         # the scene itself travels on the side stream, behind the codes in NCCL's order
@@ -424,7 +460,7 @@ class ShardedCollider:
             gather_slices(radii_buf, isz, n, self.group)
             gathered = torch.cuda.Event()
             gathered.record(self._side)
-        if self.sharded_sort:
+        if self.sort_mode == "local":
             # own windows plus one position either side (the window pass reads its neighbours' codes)
             lo, hi = max(self.q_begin, 1) - 1, min(self.q_end, n - 1)
             if self.q_end > self.q_begin:
@@ -437,12 +473,43 @@ class ShardedCollider:
         cq.wait_event(gathered)
         c._mark(cq, "broadcast", 0)      # (what is left of the scene's all-gather after the sort)
 
+    def _front_exchange(self, cq, coords_buf, radii_buf, b, e):
+        """Own codes -> top-digit counts (all-gathered: 1 KB per rank) -> push of the own spheres to the ranks
+        whose windows they fall into -> sort of what this rank received."""
+        c = self.collider
+        L, P, S = _lib.lib(), _lib.ptr, _lib.stream_ptr(cq)
+        n, code, isz, me = self.size, c.program._code, c.program.coord_dtype.itemsize, self.rank
+        own_coords, own_radii = P(coords_buf) + b * 4 * isz, P(radii_buf) + b * isz
+        if e > b:
+            _lib.check(L.col_morton(P(c._codes_bufs[0]), None, own_coords, P(c._scene_buf), code, e - b, e - b, S),
+                       "col_morton")
+        _lib.check(L.col_shard_count(P(c._codes_bufs[0]), e - b, MORTON_BITS, P(self._hist_own), S), "col_shard_count")
+        dist.all_gather_into_tensor(self._hist_all, self._hist_own, group=self.group)
+        c._mark(cq, "morton", 2)
+        _lib.check(L.col_shard_push(P(self._hist_all), self.world, me, P(self._pos_table), n, P(c._codes_bufs[0]),
+                                    e - b, b, own_coords, own_radii, code, MORTON_BITS, *self._recv_tables,
+                                    P(self._plan), P(self._push_scratch), S), "col_shard_push")
+        # every rank's pushes precede its part of this collective in stream order: past it, all have landed
+        dist.all_reduce(self._token, group=self.group)
+        c._mark(cq, "exchange", 1 + self.world)
+        if self.q_end > self.q_begin:
+            recv_codes, recv_ids = self._sb_recv[0].local, self._sb_recv[1].local
+            _lib.check(L.col_shard_sort_received(P(recv_codes), P(recv_ids), n, P(self._plan) + 32 * me, MORTON_BITS,
+                                                 P(c._codes_bufs[1]), P(c._ids_bufs[0]), P(c._ids_bufs[1]),
+                                                 P(self._recv_sort_scratch), S), "col_shard_sort_received")
+        c._mark(cq, "sort", 4 + (MORTON_BITS + 7) // 8)
+
     def _build_sharded(self, cq, coords_buf, radii_buf):
         """Own windows -> all-gather of the handed-over roots -> spanning nodes (replicated) -> halo fetch."""
         c = self.collider
         L, P, S = _lib.lib(), _lib.ptr, _lib.stream_ptr(cq)
         n, code = self.size, c.program._code
-        _lib.check(L.col_shard_build_windows(P(c._codes_bufs[1]), P(c._ids_bufs[1]), P(c._nodes_buf), P(c._wide_buf),
+        leaf_ids = c._ids_bufs[1]
+        if self.sort_mode == "exchange":
+            # the window pass finds a leaf's sphere through its PLACE in the receive buffers (the leaf records
+            # of the reference-layout Node array, which nothing reads in this mode, carry that place too)
+            leaf_ids, coords_buf, radii_buf = c._ids_bufs[0], self._sb_recv[2].local, self._sb_recv[3].local
+        _lib.check(L.col_shard_build_windows(P(c._codes_bufs[1]), P(leaf_ids), P(c._nodes_buf), P(c._wide_buf),
                                              P(c._flags_buf), P(c._bounds_buf), P(coords_buf), P(radii_buf),
                                              P(c._scene_buf), code, n, self.win_edges[self.rank],
                                              self.win_edges[self.rank + 1], P(self._packed), self._cap, S),

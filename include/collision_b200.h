@@ -347,6 +347,29 @@ int col_shard_halo(const void* gathered, uint32_t cap, uint32_t world, uint32_t 
                    const uint64_t* wide_table, const uint64_t* bounds_table, const uint32_t* win_edges,
                    uint32_t n, uint32_t leaf_begin, uint32_t leaf_end, const uint64_t* ids_table,
                    uint32_t* ids_sorted, void* stream);
+/* The same selection with the data EXCHANGED instead of replicated (no rank ever holds all the codes or the whole
+ * scene): col_shard_count = top-digit counts of the rank's own slice of the codes (hist256; the caller all-gathers
+ * them, rank-major, into hist_all); col_shard_push = the plan every rank derives from hist_all (plan: 8 words per
+ * rank {offset, count, first bucket, last bucket, where this rank's entries start in that rank's receive buffers})
+ * and, per destination, a stable compaction of the own slice's {code, sphere id = id_base + i, coordinates, radius}
+ * written straight into the destination's receive buffers (h_recv_*: HOST arrays of `world` device addresses as
+ * mapped into this process, col_ipc_open; the rank's own entry = its own buffers; each sized for n entries);
+ * pos_table: world x {pos_lo, pos_hi} (device).  The caller then runs any collective on the stream (all pushes have
+ * landed once every rank has passed it) and calls col_shard_sort_received: stable sort of the received codes --
+ * clobbered -- placed at codes_sorted + offset, with place_sorted = each entry's index in the receive buffers (the
+ * build reads coordinates and radii through it) and ids_sorted = the sphere ids; range = the rank's own plan entry.
+ * Positions [offset, offset + count) come out bit-identical to col_sort_pairs over the whole scene. */
+int col_shard_count(const uint32_t* codes_own, uint32_t n_own, uint32_t end_bit, uint32_t* hist256, void* stream);
+size_t col_shard_push_scratch_bytes(uint64_t n_own, uint32_t world);
+int col_shard_push(const uint32_t* hist_all, uint32_t world, uint32_t my_rank, const uint32_t* pos_table,
+                   uint32_t n, const uint32_t* codes_own, uint32_t n_own, uint32_t id_base,
+                   const void* coords_own, const void* radii_own, int dtype, uint32_t end_bit,
+                   const uint64_t* h_recv_codes, const uint64_t* h_recv_ids, const uint64_t* h_recv_coords,
+                   const uint64_t* h_recv_radii, uint32_t* plan, void* scratch, void* stream);
+size_t col_shard_sort_received_scratch_bytes(uint64_t n);
+int col_shard_sort_received(uint32_t* recv_codes, const uint32_t* recv_ids, uint32_t n, const uint32_t* range,
+                            uint32_t end_bit, uint32_t* codes_sorted, uint32_t* place_sorted, uint32_t* ids_sorted,
+                            void* scratch, void* stream);
 size_t col_shard_sort_scratch_bytes(uint64_t n);
 int col_shard_sort(const uint32_t* codes, uint32_t n, uint32_t pos_lo, uint32_t pos_hi, uint32_t end_bit,
                    uint32_t* codes_sorted, uint32_t* ids_sorted, uint32_t* range_out, void* scratch,

@@ -13,8 +13,11 @@ import golden_data as G
 
 pytestmark = pytest.mark.gpu
 
-# "sharded_build" alone = with the sort dealt out as well (the default); "/replicated_sort" = every rank sorts everything
-MODES = ("broadcast_tree", "replicate_build", "gather_inputs", "sharded_build", "sharded_build/replicated_sort")
+# "sharded_build" alone = the default: the sort dealt out as well, spheres pushed to the ranks that need them;
+# "/local_sort" = codes and scene all-gathered, every rank sorts its own buckets; "/replicated_sort" = ... sorts everything
+MODES = ("broadcast_tree", "replicate_build", "gather_inputs", "sharded_build", "sharded_build/local_sort",
+         "sharded_build/replicated_sort")
+SORT_VARIANTS = {"": "exchange", "local_sort": "local", "replicated_sort": "replicated"}
 
 
 def _free_port():
@@ -63,8 +66,8 @@ def _worker(rank, world, port, n, kind, mode, balance, graph, frames, raw, tmpdi
             return ct, rt
 
         col = ShardedCollider(dev, n, 8, 64, mode=mode, balance=balance, graph=graph,
-                              sharded_sort=variant != "replicated_sort")
-        assert col.sharded_sort == (mode == "sharded_build" and not variant)
+                              sharded_sort=SORT_VARIANTS[variant])
+        assert col.sort_mode == (SORT_VARIANTS[variant] if mode == "sharded_build" else "replicated")
         n_buf = torch.zeros(1, dtype=torch.int32, device=dev)
         ct, rt = inputs()
         torch.cuda.synchronize()
@@ -131,7 +134,7 @@ def test_two_ranks_equal_single_rank(tmp_path, oracle, mode, n, kind):
     _run(tmp_path, oracle, n, kind, mode)
 
 
-@pytest.mark.parametrize("mode", ["sharded_build", "sharded_build/replicated_sort"])
+@pytest.mark.parametrize("mode", ["sharded_build", "sharded_build/local_sort", "sharded_build/replicated_sort"])
 def test_two_ranks_many_windows(tmp_path, oracle, mode):
     """Enough spheres for many windows, several tiles of the collect pass and unequal buckets per rank."""
     _run(tmp_path, oracle, 300007, "skewed", mode)

@@ -19,6 +19,7 @@ def main():
     ap.add_argument("--spheres", type=int, default=20011)
     ap.add_argument("--mode", default="sharded_build")
     ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--sort", default="exchange", choices=["exchange", "local", "replicated"])
     ap.add_argument("--graph", action="store_true", help="sync_totals=False calls: plain, plain, capture, replay ...")
     args = ap.parse_args()
     import faulthandler
@@ -43,13 +44,18 @@ def main():
     want = torch.empty(max(total, 1) * 2, dtype=torch.int32, device=dev)
     one.get_collisions(cq, coords, radii, nb, want, total).synchronize()
     print("rank {} single-GPU total {}".format(rank, total), flush=True)
-    col = ShardedCollider(dev, n, 8, 128, mode=args.mode, graph=args.graph)
+    col = ShardedCollider(dev, n, 8, 128, mode=args.mode, graph=args.graph, sharded_sort=args.sort)
     print("rank {} sharded collider up: queries [{}, {})".format(rank, col.q_begin, col.q_end), flush=True)
     col.get_collisions(cq, coords.clone(), radii.clone(), nb, None, 0).synchronize()
     print("rank {} count-only: local {} base {} total {}".format(rank, col.local_pairs, col.pair_base, col.total_pairs), flush=True)
     cap = col.local_pairs
     rows = torch.empty(max(cap, 1) * 2, dtype=torch.int32, device=dev)
     cc, rr = coords.clone(), radii.clone()
+    if args.mode in ("gather_inputs", "sharded_build"):     # the rank holds its own slice only: poison the rest
+        from collision_b200.sharded import shard_range
+        b, e = shard_range(n, world, rank)
+        coords, radii = coords.clone(), radii.clone()
+        coords[:b] = float("nan"); coords[e:] = float("nan"); radii[:b] = float("nan"); radii[e:] = float("nan")
     for step in range(args.steps):
         if args.graph:
             cc.copy_(coords); rr.copy_(radii); torch.cuda.synchronize()
