@@ -703,7 +703,7 @@ def run_multi(args):
             coords_d, radii_d = (full_c.clone(), full_r.clone()) if rank == 0 else \
                 (torch.full_like(full_c, float("nan")), torch.full_like(full_r, float("nan")))
         crumb("collider + count-only call")
-        col = ShardedCollider(dev, n, 8, 128, mode=mode, graph=not args.no_graph)
+        col = ShardedCollider(dev, n, 8, 128, mode=mode, graph=not args.no_graph, sharded_sort=args.shard_sort)
         n_buf = torch.zeros(1, dtype=torch.int32, device=dev)
         cq.wait_stream(torch.cuda.current_stream())
         col.get_collisions(cq, coords_d, radii_d, n_buf, None, 0).synchronize()
@@ -725,6 +725,8 @@ def run_multi(args):
         res = dict(total_ms=float(sum(ms)), total=total, cap=cap, launches=launches, stages=st, n=n)
         # one more call WITH the host bookkeeping: local_pairs / pair_base of the timed configuration
         col.get_collisions(cq, coords_d, radii_d, n_buf, pairs_d, cap).synchronize()
+        res["sort_n"] = getattr(col, "sort_count", n)      # pairs this rank's sort moved (all of them unless the sort is dealt out)
+        res["sort_mode"] = col.sort_mode
         assert col.local_pairs == cap and col.total_pairs == total
         assert (int(n_buf.item()) & 0xFFFFFFFF) == (total & 0xFFFFFFFF)
 
@@ -835,7 +837,7 @@ def run_multi(args):
         dom = max((k for k in stages if k in STAGE_BYTES), key=lambda k: stages[k], default=None)
         roofline = None
         if dom:
-            q = n // world if dom.startswith("traverse") else n
+            q = n // world if dom.startswith("traverse") else (R["sort_n"] if dom == "sort" else n)
             m = R["cap"] if dom.startswith("traverse") else R["total"]
             nbytes = STAGE_BYTES[dom](q, m)
             roofline = {"kernel": dom, "bound": "latency" if dom.startswith(("traverse", "tree")) else "hbm",
@@ -848,8 +850,9 @@ def run_multi(args):
             "scaling": "weak" if key == "B" else "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": workload_config(key, n, {
                 "launch": "kernel by kernel" if args.no_graph else "CUDA graph replay where the mode allows it",
-                "parallelism": "{} ({} ranks): traversal sharded over contiguous Morton-sorted query ranges, "
-                               "NCCL all_gather of the row totals".format(mode, world)}),
+                "parallelism": "{} ({} ranks; sort: {}): traversal sharded over contiguous Morton-sorted query ranges, "
+                               "NCCL all_gather of the row totals".format(mode, world, R["sort_mode"]),
+                "sorted_pairs_on_rank0": R["sort_n"]}),
             "pairs": R["total"], "pairs_per_sec": R["total"] / (ms_per_step * 1e-3),
             "e2e": {"value": n / e2e_sec, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": e2e_sec * 1e3,
@@ -887,6 +890,8 @@ def main():
                     help="override the workload (default: D = configs[3] on one GPU, E = configs[4] on several)")
     ap.add_argument("--n-log2", type=int, default=None, help="override the scene size (development / CI)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
+    ap.add_argument("--shard-sort", default="exchange", choices=["exchange", "local", "replicated"],
+                    help="mode sharded_build: how the sort is dealt out (see ShardedCollider)")
     ap.add_argument("--no-stages", action="store_true", help="skip stages_at_target / config_b / weak_b (profiling runs)")
     ap.add_argument("--no-graph", action="store_true", help="enqueue kernel by kernel instead of replaying a CUDA graph")
     ap.add_argument("--time-n1", action="store_true", default=True,

@@ -554,6 +554,18 @@ pack_items_kernel(const uint32_t* __restrict__ items, const col_node* __restrict
     reinterpret_cast<PackedItem<T>*>(packed + PACK_HEADER)[k] = it;
 }
 
+// Did any rank hand over more roots than the exchange holds?  Then the spanning nodes cannot be completed, and
+// nothing may walk them (a walk over half-built records need not terminate): the top pass writes a root whose
+// children are two copies of leaf 0 behind boxes that nothing but a query spanning the whole scene overlaps, the
+// halo asks for nothing, the traversal ends at once, and the host -- which sees the same flags when it next
+// syncs -- repeats the call with larger buffers or raises.
+__device__ __forceinline__ bool shard_exchange_overflowed(const unsigned char* __restrict__ gathered, size_t stride,
+                                                          uint32_t world) {
+    uint32_t over = 0;
+    for (uint32_t r = 0; r < world; r++) over |= reinterpret_cast<const uint32_t*>(gathered + r * stride)[1];
+    return over != 0;
+}
+
 // The codes at the ends of the other ranks' roots -> their places in this rank's array of sorted codes
 // (with the sharded sort it holds the rank's own part only).  Every position the top pass reads is the
 // lo - 1 / lo / hi / hi + 1 of some root: a spanning node's range ends where two of its descendants' do.
@@ -565,6 +577,7 @@ scatter_root_codes_kernel(const unsigned char* __restrict__ gathered, uint32_t c
     const uint32_t r = (uint32_t)(t / cap), j = (uint32_t)(t % cap);
     if (r >= world || r == my_rank) return;
     const size_t stride = PACK_HEADER + (size_t)cap * sizeof(PackedItem<T>);
+    if (shard_exchange_overflowed(gathered, stride, world)) return;
     const unsigned char* theirs = gathered + r * stride;
     if (j >= min(*reinterpret_cast<const uint32_t*>(theirs), cap)) return;
     const PackedItem<T>* it = reinterpret_cast<const PackedItem<T>*>(theirs + PACK_HEADER) + j;
@@ -585,6 +598,14 @@ top_packed_kernel(const unsigned char* __restrict__ gathered, uint32_t cap, uint
     const uint32_t r = (uint32_t)(t / cap), j = (uint32_t)(t % cap);
     if (r >= world) return;
     const size_t stride = PACK_HEADER + (size_t)cap * sizeof(PackedItem<T>);
+    if (shard_exchange_overflowed(gathered, stride, world)) {
+        if (t == 0) {   // (see shard_exchange_overflowed)
+            uint4* rp = reinterpret_cast<uint4*>(wide);
+            rp[0] = make_uint4(0x80000000u, 0x80000000u, 0xFFFFFFFFu, 0xFFFFFFFFu);
+            rp[1] = make_uint4(0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu);
+        }
+        return;
+    }
     const unsigned char* mine = gathered + r * stride;
     if (j >= min(*reinterpret_cast<const uint32_t*>(mine), cap)) return;
     const PackedItem<T> it = reinterpret_cast<const PackedItem<T>*>(mine + PACK_HEADER)[j];
@@ -614,12 +635,14 @@ top_packed_kernel(const unsigned char* __restrict__ gathered, uint32_t cap, uint
 // [lo, g] and [g + 1, hi], g = the left child's index (internal) or position (leaf).
 template <typename T>
 __global__ void __launch_bounds__(256)
-halo_probe_kernel(const unsigned char* __restrict__ my_packed, uint32_t cap, const unsigned char* __restrict__ wide,
+halo_probe_kernel(const unsigned char* __restrict__ gathered, uint32_t world, const unsigned char* __restrict__ my_packed,
+                  uint32_t cap, const unsigned char* __restrict__ wide,
                   const T* __restrict__ scene, uint32_t* __restrict__ asked, uint2* __restrict__ list,
                   uint32_t* __restrict__ list_hdr, uint32_t list_cap, uint32_t n, uint32_t leaf_begin,
                   uint32_t leaf_end) {
     const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
     if (j >= min(*reinterpret_cast<const uint32_t*>(my_packed), cap)) return;
+    if (shard_exchange_overflowed(gathered, PACK_HEADER + (size_t)cap * sizeof(PackedItem<T>), world)) return;
     const PackedItem<T> it = reinterpret_cast<const PackedItem<T>*>(my_packed + PACK_HEADER)[j];
     const Quant<T> qz = make_quant(scene);
     T blo[3] = {it.box[0], it.box[1], it.box[2]}, bhi[3] = {it.box[3], it.box[4], it.box[5]};
@@ -898,10 +921,12 @@ COL_API int col_shard_halo(const void* gathered, uint32_t cap, uint32_t world, u
     uint32_t* asked = flags + n;
     const unsigned pblocks = col_blocks(cap, 256);
     if (dtype == COL_F32)
-        halo_probe_kernel<float><<<pblocks, 256, 0, s>>>(mine, cap, (const unsigned char*)wide, (const float*)scene2x4, asked,
+        halo_probe_kernel<float><<<pblocks, 256, 0, s>>>((const unsigned char*)gathered, world, mine, cap,
+                                                         (const unsigned char*)wide, (const float*)scene2x4, asked,
                                                          entries, hdr, list_cap, n, leaf_begin, leaf_end);
     else
-        halo_probe_kernel<double><<<pblocks, 256, 0, s>>>(mine, cap, (const unsigned char*)wide, (const double*)scene2x4,
+        halo_probe_kernel<double><<<pblocks, 256, 0, s>>>((const unsigned char*)gathered, world, mine, cap,
+                                                          (const unsigned char*)wide, (const double*)scene2x4,
                                                           asked, entries, hdr, list_cap, n, leaf_begin, leaf_end);
     COL_CHECK_LAUNCH();
     halo_fetch_kernel<<<COL_NUM_SMS * 8, 256, 0, s>>>(entries, hdr, list_cap, (const unsigned long long*)wide_table,

@@ -805,6 +805,7 @@ collect_push_kernel(const uint32_t* __restrict__ codes, uint32_t n, uint32_t id_
     __shared__ unsigned s_tile;
     __shared__ uint32_t s_warp_total[COLLECT_THREADS / 32];
     __shared__ uint32_t s_tile_prefix;
+    __shared__ unsigned short s_off[COLLECT_TILE];
     if (threadIdx.x == 0) s_tile = atomicAdd(ticket, 1u);
     __syncthreads();
     const unsigned tile = s_tile;
@@ -884,29 +885,30 @@ collect_push_kernel(const uint32_t* __restrict__ codes, uint32_t n, uint32_t id_
         if (lane == 0) s_tile_prefix = (uint32_t)prefix;
     }
     __syncthreads();
-    const uint32_t base = out0 + s_tile_prefix + warp_prefix;
+    // the tile's collected entries, in order, as offsets into the tile: consecutive threads then write
+    // consecutive entries, so that what crosses NVLink are full lines, not 4- and 16-byte pieces
 #pragma unroll
     for (int k = 0; k < COLLECT_VECS; k++) {
-        const uint32_t e = warp_base + (uint32_t)(k * 32 + lane) * 4;
-        uint32_t dst = base + excl[k];
+        const uint32_t e = warp * COLLECT_WARP_ITEMS + (uint32_t)(k * 32 + lane) * 4;
+        uint32_t p = warp_prefix + excl[k];
         const uint32_t m = sel[k];
-        const uint32_t cv[4] = {v[k].x, v[k].y, v[k].z, v[k].w};
 #pragma unroll
-        for (int h = 0; h < 4; h++) {
-            if (m & (1u << h)) {
-                const uint32_t src = e + h;
+        for (int h = 0; h < 4; h++)
+            if (m & (1u << h)) s_off[p++] = (unsigned short)(e + h);
+    }
+    __syncthreads();
+    const uint32_t base = out0 + s_tile_prefix;
 #ifdef COL_DEBUG
-                if (dst >= plan[1]) __trap();   // more than the destination's buckets hold
+    if (tile_total && base + tile_total > plan[1]) __trap();   // more than the destination's buckets hold
 #endif
-                dst_codes[dst] = cv[h];
-                dst_ids[dst] = id_base + src;
+    for (uint32_t p = threadIdx.x; p < tile_total; p += COLLECT_THREADS) {
+        const uint32_t src = tile_base + s_off[p], dst = base + p;
+        dst_codes[dst] = __ldg(codes + src);
+        dst_ids[dst] = id_base + src;
 #pragma unroll
-                for (int w = 0; w < W; w++) {
-                    dst_coords[(size_t)dst * W + w] = ld_stream_u4(coords + (size_t)src * W + w);
-                    dst_radii[(size_t)dst * W + w] = ld_stream_u32(radii + (size_t)src * W + w);
-                }
-                dst++;
-            }
+        for (int w = 0; w < W; w++) {
+            dst_coords[(size_t)dst * W + w] = ld_stream_u4(coords + (size_t)src * W + w);
+            dst_radii[(size_t)dst * W + w] = ld_stream_u32(radii + (size_t)src * W + w);
         }
     }
 }

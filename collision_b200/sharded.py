@@ -300,19 +300,40 @@ class ShardedCollider:
         nb = L.col_shard_packed_bytes(self._cap, c.program._code)
         self._packed = _lib.alloc_bytes(ctx, nb)
         self._gathered = _lib.alloc_bytes(ctx, nb * k)
+        # what actually travels: after every call that syncs, the exchange is cut down to 1.5 x the most roots any
+        # rank handed over (+ 1024) -- the all-gather moves whole buffers, used or not.  Identical on every rank
+        # (derived from the gathered headers).
+        self._send_cap = self._cap
+        self.sort_count = n           # pairs this rank sorted in the last call that synced
         self._list = _lib.alloc_bytes(ctx, L.col_shard_list_bytes(self._list_cap))
         self._win_edges_dev = torch.tensor(self.win_edges, dtype=torch.int32, device=ctx)
         self._side = torch.cuda.Stream(_lib.device_of(ctx))
         dist.barrier(group=self.group)
 
+    def _packed_bytes(self):
+        return _lib.lib().col_shard_packed_bytes(self._send_cap, self.collider.program._code)
+
     def _check_shard_overflow(self):
+        """After a call that synced.  Returns True when the call has to be repeated (the cut-down exchange was
+        too small for this frame: it is reset to the full buffers first)."""
         hdr = self._gathered.view(torch.int32)
-        stride = self._packed.numel() // 4
-        over = any(int(hdr[r * stride + 1].item()) for r in range(self.world)) or \
-            int(self._list.view(torch.int32)[1].item())
-        if over:
+        stride = self._packed_bytes() // 4
+        heads = torch.stack([hdr[r * stride:r * stride + 2] for r in range(self.world)]).tolist()
+        over_roots = any(h[1] for h in heads)
+        over_list = bool(int(self._list.view(torch.int32)[1].item()))
+        if over_roots and self._send_cap < self._cap:
+            self._send_cap = self._cap
+            return True
+        if over_roots or over_list:
             raise RuntimeError("sharded_build: more subtree roots / remote subtrees than the exchange buffers hold "
                                "(cap {}, list {}); use mode 'gather_inputs' for this scene".format(self._cap, self._list_cap))
+        most = max(h[0] for h in heads)
+        self._send_cap = min(self._cap, max(self._send_cap if self._send_cap < self._cap else 0, most + most // 2 + 1024))
+        if self.sort_mode == "exchange":
+            self.sort_count = int(self._plan[8 * self.rank + 1].item())
+        elif self.sort_mode == "local":
+            self.sort_count = int(self._sort_range[1].item())
+        return False
 
     def close(self):
         """Collective teardown: drops the captured graphs (they hold NCCL work) and unmaps / frees the
@@ -383,7 +404,8 @@ class ShardedCollider:
         use_graph = self.graph and not sync_totals and c.stage_events is None
         if use_graph:
             key = (cq.cuda_stream, self.size, n_collisions, self.q_begin, self.q_end, _lib.ptr(coords_buf),
-                   _lib.ptr(radii_buf), _lib.ptr(n_collisions_buf), _lib.ptr(collisions_buf), c._trv_scratch_bytes)
+                   _lib.ptr(radii_buf), _lib.ptr(n_collisions_buf), _lib.ptr(collisions_buf), c._trv_scratch_bytes,
+                   getattr(self, "_send_cap", 0))
             entry = self._graphs.get(key)
             if entry is None and self._graph_candidate == key:
                 # second call with this signature (scratch allocated, NCCL communicator warm): capture
@@ -411,8 +433,10 @@ class ShardedCollider:
             self.local_pairs = t[self.rank]
             self.pair_base = sum(t[:self.rank])
             self.total_pairs = sum(t)
-            if self.mode == "sharded_build":
-                self._check_shard_overflow()
+            if self.mode == "sharded_build" and self._check_shard_overflow():
+                # (every rank takes this branch together: the decision comes from the gathered headers)
+                return self.get_collisions(cq, coords_buf, radii_buf, n_collisions_buf, collisions_buf, n_collisions,
+                                           None, True)
             if n_collisions > 0:
                 self.overflowed = self.local_pairs > n_collisions
                 if self.balance:     # (count-only calls never move the cuts: see __init__)
@@ -512,16 +536,17 @@ class ShardedCollider:
         _lib.check(L.col_shard_build_windows(P(c._codes_bufs[1]), P(leaf_ids), P(c._nodes_buf), P(c._wide_buf),
                                              P(c._flags_buf), P(c._bounds_buf), P(coords_buf), P(radii_buf),
                                              P(c._scene_buf), code, n, self.win_edges[self.rank],
-                                             self.win_edges[self.rank + 1], P(self._packed), self._cap, S),
+                                             self.win_edges[self.rank + 1], P(self._packed), self._send_cap, S),
                    "col_shard_build_windows")
         c._mark(cq, "build_windows", 2)
-        dist.all_gather_into_tensor(self._gathered, self._packed, group=self.group)
+        nb = self._packed_bytes()
+        dist.all_gather_into_tensor(self._gathered[:nb * self.world], self._packed[:nb], group=self.group)
         c._mark(cq, "gather_roots", 0)
-        _lib.check(L.col_shard_top(P(self._gathered), self._cap, self.world, self.rank, P(c._codes_bufs[1]),
+        _lib.check(L.col_shard_top(P(self._gathered), self._send_cap, self.world, self.rank, P(c._codes_bufs[1]),
                                    P(c._nodes_buf), P(c._wide_buf), P(c._flags_buf), P(c._bounds_buf),
                                    P(c._scene_buf), code, n, S), "col_shard_top")
         c._mark(cq, "build_top", 1)
-        _lib.check(L.col_shard_halo(P(self._gathered), self._cap, self.world, self.rank, P(c._wide_buf),
+        _lib.check(L.col_shard_halo(P(self._gathered), self._send_cap, self.world, self.rank, P(c._wide_buf),
                                     P(c._bounds_buf), P(c._scene_buf), code, P(c._flags_buf), P(self._list),
                                     self._list_cap, P(self._sb_wide.table), P(self._sb_bounds.table),
                                     P(self._win_edges_dev), n, self.q_begin, self.q_end,

@@ -17,7 +17,7 @@ pytestmark = pytest.mark.gpu
 # "/local_sort" = codes and scene all-gathered, every rank sorts its own buckets; "/replicated_sort" = ... sorts everything
 MODES = ("broadcast_tree", "replicate_build", "gather_inputs", "sharded_build", "sharded_build/local_sort",
          "sharded_build/replicated_sort")
-SORT_VARIANTS = {"": "exchange", "local_sort": "local", "replicated_sort": "replicated"}
+SORT_VARIANTS = {"": "exchange", "local_sort": "local", "replicated_sort": "replicated", "tiny_send": "exchange"}
 
 
 def _free_port():
@@ -68,6 +68,8 @@ def _worker(rank, world, port, n, kind, mode, balance, graph, frames, raw, tmpdi
         col = ShardedCollider(dev, n, 8, 64, mode=mode, balance=balance, graph=graph,
                               sharded_sort=SORT_VARIANTS[variant])
         assert col.sort_mode == (SORT_VARIANTS[variant] if mode == "sharded_build" else "replicated")
+        if variant == "tiny_send":      # a root exchange cut down too far: the call notices, resets it and repeats itself
+            col._send_cap = 16
         n_buf = torch.zeros(1, dtype=torch.int32, device=dev)
         ct, rt = inputs()
         torch.cuda.synchronize()
@@ -138,6 +140,10 @@ def test_two_ranks_equal_single_rank(tmp_path, oracle, mode, n, kind):
 def test_two_ranks_many_windows(tmp_path, oracle, mode):
     """Enough spheres for many windows, several tiles of the collect pass and unequal buckets per rank."""
     _run(tmp_path, oracle, 300007, "skewed", mode)
+
+
+def test_two_ranks_root_exchange_too_small(tmp_path, oracle):
+    _run(tmp_path, oracle, 20011, "uniform", "sharded_build/tiny_send")
 
 
 @pytest.mark.parametrize("mode", ["gather_inputs", "sharded_build"])

@@ -20,6 +20,7 @@ def main():
     ap.add_argument("--mode", default="sharded_build")
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--sort", default="exchange", choices=["exchange", "local", "replicated"])
+    ap.add_argument("--tiny-send", action="store_true", help="start with a root exchange that is far too small (the call must repeat itself)")
     ap.add_argument("--graph", action="store_true", help="sync_totals=False calls: plain, plain, capture, replay ...")
     args = ap.parse_args()
     import faulthandler
@@ -45,6 +46,8 @@ def main():
     one.get_collisions(cq, coords, radii, nb, want, total).synchronize()
     print("rank {} single-GPU total {}".format(rank, total), flush=True)
     col = ShardedCollider(dev, n, 8, 128, mode=args.mode, graph=args.graph, sharded_sort=args.sort)
+    if args.tiny_send:
+        col._send_cap = 16
     print("rank {} sharded collider up: queries [{}, {})".format(rank, col.q_begin, col.q_end), flush=True)
     col.get_collisions(cq, coords.clone(), radii.clone(), nb, None, 0).synchronize()
     print("rank {} count-only: local {} base {} total {}".format(rank, col.local_pairs, col.pair_base, col.total_pairs), flush=True)
@@ -69,6 +72,7 @@ def main():
         print("rank {} step {} rows equal: {}".format(rank, step, ok), flush=True)
     if args.mode == "sharded_build":
         lst = col._list.view(torch.int32)
+        print("rank {} root exchange cut to {} of {}".format(rank, col._send_cap, col._cap), flush=True)
         print("rank {} roots packed {} of cap {}, remote subtrees fetched {} of {}".format(
             rank, int(col._packed.view(torch.int32)[0].item()), col._cap, int(lst[0].item()), col._list_cap), flush=True)
     col.close()
