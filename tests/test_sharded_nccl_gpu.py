@@ -36,13 +36,16 @@ def _scene(n, kind):
     return c, np.ascontiguousarray(r, dtype=np.float32)
 
 
-def _worker(rank, world, port, n, kind, mode, balance, graph, frames, raw, tmpdir):
+def _worker(rank, world, port, n, kind, mode, balance, graph, frames, raw, tmpdir, one_device=False):
     import torch
     import torch.distributed as dist
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
-    dev = torch.device("cuda", rank)
+    dev = torch.device("cuda", 0 if one_device else rank)
     torch.cuda.set_device(dev)
-    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    if one_device:      # every rank on the same GPU: gloo moves the collectives' bytes, CUDA IPC maps the peers' buffers
+        dist.init_process_group("gloo", rank=rank, world_size=world)
+    else:
+        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
     try:
         from collision_b200.sharded import ShardedCollider, shard_range
         mode, _, variant = mode.partition("/")
@@ -107,25 +110,26 @@ def _worker(rank, world, port, n, kind, mode, balance, graph, frames, raw, tmpdi
         dist.destroy_process_group()
 
 
-def _run(tmp_path, oracle, n, kind, mode, balance=False, graph=False, frames=1, raw=False):
+def _run(tmp_path, oracle, n, kind, mode, balance=False, graph=False, frames=1, raw=False, world=2, one_device=False):
     import torch
     import torch.multiprocessing as mp
-    if not torch.cuda.is_available() or torch.cuda.device_count() < 2:
-        pytest.skip("needs 2 GPUs")
+    if not torch.cuda.is_available() or (not one_device and torch.cuda.device_count() < world):
+        pytest.skip("needs {} GPUs".format(world))
     from collision_b200.sharded import ShardedCollider
     if mode.partition("/")[0] not in ShardedCollider.MODES:
         pytest.skip("mode {} not built".format(mode))
-    world = 2
-    mp.spawn(_worker, args=(world, _free_port(), n, kind, mode, balance, graph, frames, raw, str(tmp_path)),
+    mp.spawn(_worker, args=(world, _free_port(), n, kind, mode, balance, graph, frames, raw, str(tmp_path), one_device),
              nprocs=world, join=True)
     c, r = _scene(n, kind)
     want = oracle.collide(c, r)
     logs = [np.load(tmp_path / "log{}.npy".format(k)) for k in range(world)]
     for f in range(frames):
         parts = [np.load(tmp_path / "rows{}_{}.npy".format(f, k)) for k in range(world)]
-        assert logs[0][f][1] == 0 and logs[1][f][1] == logs[0][f][0]          # bases = running totals
+        for k in range(world):                                                # bases = running totals, ranges tile [0, n)
+            assert logs[k][f][1] == sum(logs[j][f][0] for j in range(k))
+            assert logs[k][f][3] == (logs[k - 1][f][4] if k else 0)
+        assert logs[-1][f][4] == n
         assert all(l[f][2] == want["total"] for l in logs)
-        assert logs[0][f][3] == 0 and logs[0][f][4] == logs[1][f][3] and logs[1][f][4] == n
         np.testing.assert_equal(np.concatenate(parts), want["pairs"])        # rank-major == single rank, in ORDER
     return logs
 
@@ -163,3 +167,24 @@ def test_two_ranks_balanced(tmp_path, oracle, mode):
 @pytest.mark.parametrize("mode", MODES)
 def test_two_ranks_graph_replay(tmp_path, oracle, mode):
     _run(tmp_path, oracle, 20011, "uniform", mode, graph=True, frames=4)
+
+
+# ---- the same ranks, all on ONE GPU (gloo for the collectives, CUDA IPC between the processes): runs on a one-GPU
+# box, and with more ranks than the 2-GPU tests above -- middle ranks, three owners to fetch from
+@pytest.mark.parametrize("mode", MODES)
+def test_three_ranks_on_one_device(tmp_path, oracle, mode):
+    _run(tmp_path, oracle, 60013, "skewed", mode, world=3, one_device=True)
+
+
+@pytest.mark.parametrize("mode", [m for m in MODES if m.startswith("sharded_build")])
+def test_four_ranks_on_one_device(tmp_path, oracle, mode):
+    _run(tmp_path, oracle, 60013, "skewed", mode, world=4, one_device=True)
+
+
+@pytest.mark.parametrize("mode", ["sharded_build", "sharded_build/local_sort"])
+def test_five_ranks_on_one_device_duplicates(tmp_path, oracle, mode):
+    _run(tmp_path, oracle, 16384, "duplicates", mode, world=5, one_device=True)
+
+
+def test_four_ranks_on_one_device_root_exchange_too_small(tmp_path, oracle):
+    _run(tmp_path, oracle, 60013, "uniform", "sharded_build/tiny_send", world=4, one_device=True)

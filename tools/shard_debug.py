@@ -20,15 +20,20 @@ def main():
     ap.add_argument("--mode", default="sharded_build")
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--sort", default="exchange", choices=["exchange", "local", "replicated"])
+    ap.add_argument("--one-device", action="store_true", help="every rank on cuda:0, gloo for the collectives (cheap multi-rank "
+                    "check of the kernels and the peer mappings on a one-GPU box; no graph capture)")
     ap.add_argument("--tiny-send", action="store_true", help="start with a root exchange that is far too small (the call must repeat itself)")
     ap.add_argument("--graph", action="store_true", help="sync_totals=False calls: plain, plain, capture, replay ...")
     args = ap.parse_args()
     import faulthandler
     faulthandler.dump_traceback_later(90, exit=True)      # a hang shows where
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
-    dev = torch.device("cuda", int(os.environ.get("LOCAL_RANK", "0")))
+    dev = torch.device("cuda", 0 if args.one_device else int(os.environ.get("LOCAL_RANK", "0")))
     torch.cuda.set_device(dev)
-    dist.init_process_group("nccl", device_id=dev, timeout=datetime.timedelta(seconds=60))
+    if args.one_device:
+        dist.init_process_group("gloo", timeout=datetime.timedelta(seconds=60))
+    else:
+        dist.init_process_group("nccl", device_id=dev, timeout=datetime.timedelta(seconds=60))
     from collision_b200.collision import Collider
     from collision_b200.sharded import ShardedCollider
     n = args.spheres
@@ -49,8 +54,12 @@ def main():
     if args.tiny_send:
         col._send_cap = 16
     print("rank {} sharded collider up: queries [{}, {})".format(rank, col.q_begin, col.q_end), flush=True)
-    col.get_collisions(cq, coords.clone(), radii.clone(), nb, None, 0).synchronize()
-    print("rank {} count-only: local {} base {} total {}".format(rank, col.local_pairs, col.pair_base, col.total_pairs), flush=True)
+    for again in range(2):
+        cc0, rr0 = coords.clone(), radii.clone()
+        torch.cuda.synchronize()        # (the clones are made on the default stream)
+        col.get_collisions(cq, cc0, rr0, nb, None, 0).synchronize()
+        print("rank {} count-only: local {} base {} total {} (totals {}, root exchange {})".format(
+            rank, col.local_pairs, col.pair_base, col.total_pairs, col._totals.tolist(), getattr(col, "_send_cap", None)), flush=True)
     cap = col.local_pairs
     rows = torch.empty(max(cap, 1) * 2, dtype=torch.int32, device=dev)
     cc, rr = coords.clone(), radii.clone()
@@ -67,9 +76,22 @@ def main():
             t = col._totals.tolist()
             col.total_pairs, col.pair_base = sum(t), sum(t[:rank])
         else:
-            col.get_collisions(cq, coords.clone(), radii.clone(), nb, rows, cap).synchronize()
-        ok = col.total_pairs == total and bool((rows[:cap * 2] == want[col.pair_base * 2:(col.pair_base + cap) * 2]).all())
-        print("rank {} step {} rows equal: {}".format(rank, step, ok), flush=True)
+            cc1, rr1 = coords.clone(), radii.clone()
+            torch.cuda.synchronize()
+            col.get_collisions(cq, cc1, rr1, nb, rows, cap).synchronize()
+        t = col._totals.tolist()
+        mine = min(t[rank], cap)
+        got = rows[:mine * 2].view(-1, 2)
+        ref = want[col.pair_base * 2:(col.pair_base + mine) * 2].view(-1, 2)
+        ok = col.total_pairs == total and t[rank] == cap and got.shape == ref.shape and bool((got == ref).all())
+        print("rank {} step {} rows equal: {} (totals {}, count-only said {})".format(rank, step, ok, t, cap), flush=True)
+        if not ok and got.shape == ref.shape:
+            bad = (got != ref).any(dim=1).nonzero().flatten()
+            print("rank {}: {} rows differ, first at {}: got {} want {}; next rows got {} want {}".format(
+                rank, bad.numel(), int(bad[0]) if bad.numel() else -1,
+                got[bad[0]].tolist() if bad.numel() else None, ref[bad[0]].tolist() if bad.numel() else None,
+                got[bad[0]:bad[0] + 3].tolist() if bad.numel() else None,
+                ref[bad[0]:bad[0] + 3].tolist() if bad.numel() else None), flush=True)
     if args.mode == "sharded_build":
         lst = col._list.view(torch.int32)
         print("rank {} root exchange cut to {} of {}".format(rank, col._send_cap, col._cap), flush=True)
