@@ -562,8 +562,20 @@ pack_items_kernel(const uint32_t* __restrict__ items, const col_node* __restrict
 __device__ __forceinline__ bool shard_exchange_overflowed(const unsigned char* __restrict__ gathered, size_t stride,
                                                           uint32_t world) {
     uint32_t over = 0;
-    for (uint32_t r = 0; r < world; r++) over |= reinterpret_cast<const uint32_t*>(gathered + r * stride)[1];
+    for (uint32_t r = 0; r < world; r++) {
+        const uint32_t* h = reinterpret_cast<const uint32_t*>(gathered + r * stride);
+        over |= h[1] | h[3];   // {roots, roots overflow (or the rank's probe list), spanning nodes, their overflow}
+    }
     return over != 0;
+}
+
+// What a rank puts into the all-gather: a 64-byte header {roots, overflow, spanning nodes, overflow}, up to XCHG_ROOTS
+// roots of its maximal subtrees that stay inside its own range of leaves (PackedItem), and the indices of the nodes
+// it built ABOVE its windows (they span windows, but not ranks): the other ranks copy those records from its HBM.
+constexpr uint32_t XCHG_HEADER = 64;
+constexpr uint32_t XCHG_ROOTS = 2048;   // (a range has at most two such subtrees per level of the tree)
+template <typename T> __host__ __device__ constexpr size_t xchg_span_offset() {
+    return XCHG_HEADER + (size_t)XCHG_ROOTS * sizeof(PackedItem<T>);
 }
 
 // The codes at the ends of the other ranks' roots -> their places in this rank's array of sorted codes
@@ -571,12 +583,11 @@ __device__ __forceinline__ bool shard_exchange_overflowed(const unsigned char* _
 // lo - 1 / lo / hi / hi + 1 of some root: a spanning node's range ends where two of its descendants' do.
 template <typename T>
 __global__ void __launch_bounds__(256)
-scatter_root_codes_kernel(const unsigned char* __restrict__ gathered, uint32_t cap, uint32_t world, uint32_t my_rank,
-                          uint32_t* __restrict__ codes, uint32_t n) {
+scatter_root_codes_kernel(const unsigned char* __restrict__ gathered, size_t stride, uint32_t cap, uint32_t world,
+                          uint32_t my_rank, uint32_t* __restrict__ codes, uint32_t n) {
     const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const uint32_t r = (uint32_t)(t / cap), j = (uint32_t)(t % cap);
     if (r >= world || r == my_rank) return;
-    const size_t stride = PACK_HEADER + (size_t)cap * sizeof(PackedItem<T>);
     if (shard_exchange_overflowed(gathered, stride, world)) return;
     const unsigned char* theirs = gathered + r * stride;
     if (j >= min(*reinterpret_cast<const uint32_t*>(theirs), cap)) return;
@@ -591,13 +602,13 @@ scatter_root_codes_kernel(const unsigned char* __restrict__ gathered, uint32_t c
 // top pass over the gathered roots of ALL ranks (replicated on every rank)
 template <typename T>
 __global__ void __launch_bounds__(256)
-top_packed_kernel(const unsigned char* __restrict__ gathered, uint32_t cap, uint32_t world, uint32_t my_rank,
-                  const uint32_t* __restrict__ codes, col_node* __restrict__ nodes, unsigned char* __restrict__ wide,
-                  uint32_t* __restrict__ flags, T* __restrict__ bounds, const T* __restrict__ scene, uint32_t n) {
+top_packed_kernel(const unsigned char* __restrict__ gathered, size_t stride, uint32_t cap, uint32_t world,
+                  uint32_t my_rank, const uint32_t* __restrict__ codes, col_node* __restrict__ nodes,
+                  unsigned char* __restrict__ wide, uint32_t* __restrict__ flags, T* __restrict__ bounds,
+                  const T* __restrict__ scene, uint32_t n) {
     const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const uint32_t r = (uint32_t)(t / cap), j = (uint32_t)(t % cap);
     if (r >= world) return;
-    const size_t stride = PACK_HEADER + (size_t)cap * sizeof(PackedItem<T>);
     if (shard_exchange_overflowed(gathered, stride, world)) {
         if (t == 0) {   // (see shard_exchange_overflowed)
             uint4* rp = reinterpret_cast<uint4*>(wide);
@@ -635,14 +646,14 @@ top_packed_kernel(const unsigned char* __restrict__ gathered, uint32_t cap, uint
 // [lo, g] and [g + 1, hi], g = the left child's index (internal) or position (leaf).
 template <typename T>
 __global__ void __launch_bounds__(256)
-halo_probe_kernel(const unsigned char* __restrict__ gathered, uint32_t world, const unsigned char* __restrict__ my_packed,
-                  uint32_t cap, const unsigned char* __restrict__ wide,
+halo_probe_kernel(const unsigned char* __restrict__ gathered, size_t stride, uint32_t world,
+                  const unsigned char* __restrict__ my_packed, uint32_t cap, const unsigned char* __restrict__ wide,
                   const T* __restrict__ scene, uint32_t* __restrict__ asked, uint2* __restrict__ list,
                   uint32_t* __restrict__ list_hdr, uint32_t list_cap, uint32_t n, uint32_t leaf_begin,
                   uint32_t leaf_end) {
     const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
     if (j >= min(*reinterpret_cast<const uint32_t*>(my_packed), cap)) return;
-    if (shard_exchange_overflowed(gathered, PACK_HEADER + (size_t)cap * sizeof(PackedItem<T>), world)) return;
+    if (shard_exchange_overflowed(gathered, stride, world)) return;
     const PackedItem<T> it = reinterpret_cast<const PackedItem<T>*>(my_packed + PACK_HEADER)[j];
     const Quant<T> qz = make_quant(scene);
     T blo[3] = {it.box[0], it.box[1], it.box[2]}, bhi[3] = {it.box[3], it.box[4], it.box[5]};
@@ -652,7 +663,13 @@ halo_probe_kernel(const unsigned char* __restrict__ gathered, uint32_t world, co
     int sp = 0;
     uint32_t idx = 0, lo = 0, hi = leaf_start;
     if ((lo >> 8) == (hi >> 8)) return;   // a single window: nothing spans windows
+#ifdef COL_DEBUG
+    uint32_t visits = 0;
+#endif
     while (true) {
+#ifdef COL_DEBUG   // a walk over half-built spanning nodes need not end: trap instead of hanging
+        if (++visits > 2u * n || idx >= leaf_start || lo > hi || hi > leaf_start) __trap();
+#endif
         const uint4* rp = reinterpret_cast<const uint4*>(wide + (size_t)idx * QNODE_BYTES);
         const uint4 r0 = rp[0], r1 = rp[1];
         const bool la = (int32_t)r0.x < 0, lb = (int32_t)r0.y < 0;
@@ -732,6 +749,108 @@ halo_fetch_kernel(const uint2* __restrict__ list, const uint32_t* __restrict__ l
         if (ids_table) {   // sharded sort: the sphere ids of those leaves are the owner's to give, too
             const uint32_t* src_i = reinterpret_cast<const uint32_t*>(ids_table[owner]);
             for (uint32_t k = ent.x + lane; k <= ent.y; k += 32) ids[k] = ld_relaxed_u32(src_i + k);
+        }
+    }
+}
+
+// ---- the nodes above the windows, two levels (sharded build).  LOCAL: a rank climbs from the roots its own
+// windows handed over, as long as the parent still lies inside its own range of leaves [leaf_begin, leaf_end) --
+// known from the node alone, like the window test: the parent reaches past the range's end iff the code just
+// beyond it shares at least the parent's prefix.  Where it does, the subtree is one of the rank's (few) RANGE
+// ROOTS and goes into the exchange; every node finished on the way is listed there by index.  GLOBAL
+// (top_packed_kernel over the gathered range roots): the handful of nodes that span ranks, on every rank.
+template <typename T>
+__global__ void __launch_bounds__(256)
+top_local_kernel(const uint32_t* __restrict__ codes, col_node* __restrict__ nodes, unsigned char* __restrict__ wide,
+                 uint32_t* __restrict__ flags, const uint32_t* __restrict__ items, T* __restrict__ bounds,
+                 const T* __restrict__ scene, uint32_t n, uint32_t leaf_begin, uint32_t leaf_end,
+                 const unsigned char* __restrict__ probe, unsigned char* __restrict__ xchg, uint32_t span_cap) {
+    const uint32_t t = leaf_begin + blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t* hdr = reinterpret_cast<uint32_t*>(xchg);
+    // a probe list that overflowed leaves the halo incomplete: everybody has to know (see shard_exchange_overflowed)
+    if (t == leaf_begin && reinterpret_cast<const uint32_t*>(probe)[1]) hdr[1] = 1u;
+    if (t >= leaf_end) return;
+    uint32_t self = items[t];
+    if (self == NO_ARRIVAL) return;
+    const Quant<T> qz = make_quant(scene);
+    const uint32_t leaf_start = n - 1;
+    uint32_t lo, hi;
+    if (self >= leaf_start) {
+        lo = hi = self - leaf_start;
+    } else {
+        const uint2 rec = *reinterpret_cast<const uint2*>(nodes + self);   // {lo (window pass), right_edge}
+        lo = rec.x;
+        hi = rec.y;
+    }
+    Box<T> box = load_box_cg(bounds, self);
+    uint3 grid = quantise_box(qz, box.lo, box.hi);
+    uint32_t code_lo = __ldg(codes + lo), code_hi = __ldg(codes + hi);
+    int dl = lo > 0 ? key_delta(lo - 1, __ldg(codes + lo - 1), lo, code_lo) : -1;
+    int dr = hi < leaf_start ? key_delta(hi, code_hi, hi + 1, __ldg(codes + hi + 1)) : -1;
+    const uint32_t code_before = leaf_begin > 0 ? __ldg(codes + leaf_begin - 1) : 0u;
+    const uint32_t code_after = leaf_end < n ? __ldg(codes + leaf_end) : 0u;
+    uint32_t* span = reinterpret_cast<uint32_t*>(xchg + xchg_span_offset<T>());
+    while (true) {
+        const bool is_left = dr > dl;
+        const bool inside = is_left ? (leaf_end >= n || key_delta(hi, code_hi, leaf_end, code_after) < dr)
+                                    : (leaf_begin == 0 || key_delta(leaf_begin - 1, code_before, lo, code_lo) < dl);
+        if (!inside) {   // a range root
+            const uint32_t k = atomicAdd(hdr, 1u);
+            if (k >= XCHG_ROOTS) { hdr[1] = 1u; return; }
+            PackedItem<T> it;
+            it.self = self; it.lo = lo; it.hi = hi; it.pad = 0;
+            it.code[0] = lo > 0 ? __ldg(codes + lo - 1) : 0u;
+            it.code[1] = code_lo;
+            it.code[2] = code_hi;
+            it.code[3] = hi < leaf_start ? __ldg(codes + hi + 1) : 0u;
+#pragma unroll
+            for (int c = 0; c < 3; c++) { it.box[c] = box.lo[c]; it.box[3 + c] = box.hi[c]; }
+            reinterpret_cast<PackedItem<T>*>(xchg + XCHG_HEADER)[k] = it;
+            return;
+        }
+        const uint32_t split = is_left ? hi : lo - 1;
+        const uint32_t far_end = exchange_acq_rel(flags + split, is_left ? lo : hi);
+        if (far_end == NO_ARRIVAL) return;  // first to arrive: the sibling carries on
+        uint32_t sibling;
+        if (is_left) {
+            sibling = far_end == split + 1 ? leaf_start + split + 1 : split + 1;
+            hi = far_end;
+            code_hi = __ldg(codes + hi);
+            dr = hi < leaf_start ? key_delta(hi, code_hi, hi + 1, __ldg(codes + hi + 1)) : -1;
+        } else {
+            sibling = far_end == split ? leaf_start + split : split;
+            lo = far_end;
+            code_lo = __ldg(codes + lo);
+            dl = lo > 0 ? key_delta(lo - 1, __ldg(codes + lo - 1), lo, code_lo) : -1;
+        }
+        const Box<T> other = load_box_cg(bounds, sibling);
+        const uint3 other_grid = quantise_box(qz, other.lo, other.hi);
+        self = finish_node(nodes, wide, bounds, leaf_start, lo, hi, dl, dr, is_left, self, sibling, box, other, grid, other_grid);
+        {
+            const uint32_t k = atomicAdd(hdr + 2, 1u);
+            if (k < span_cap) span[k] = self;
+            else hdr[3] = 1u;
+        }
+        if (lo == 0 && hi == leaf_start) return;
+    }
+}
+
+// the other ranks' spanning nodes (by their lists) -> my copy of the records, from the owners' HBM
+template <typename T>
+__global__ void __launch_bounds__(256)
+fetch_spanning_kernel(const unsigned char* __restrict__ gathered, size_t stride, uint32_t span_cap, uint32_t world,
+                      uint32_t my_rank, const unsigned long long* __restrict__ wide_table, unsigned char* __restrict__ wide) {
+    if (shard_exchange_overflowed(gathered, stride, world)) return;
+    for (uint32_t r = 0; r < world; r++) {
+        if (r == my_rank) continue;
+        const unsigned char* theirs = gathered + r * stride;
+        const uint32_t count = min(reinterpret_cast<const uint32_t*>(theirs)[2], span_cap);
+        const uint32_t* list = reinterpret_cast<const uint32_t*>(theirs + xchg_span_offset<T>());
+        const unsigned char* src = reinterpret_cast<const unsigned char*>(wide_table[r]);
+        // two threads per 32-byte record
+        for (uint32_t k = blockIdx.x * blockDim.x + threadIdx.x; k < 2 * count; k += gridDim.x * blockDim.x) {
+            const size_t off = (size_t)list[k >> 1] * QNODE_BYTES + (k & 1u) * 16;
+            *reinterpret_cast<uint4*>(wide + off) = ld_cg_u4(reinterpret_cast<const uint4*>(src + off));
         }
     }
 }
@@ -876,56 +995,93 @@ COL_API int col_shard_build_windows(const uint32_t* codes_sorted, const uint32_t
     return 0;
 }
 
-COL_API int col_shard_top(const void* gathered, uint32_t cap, uint32_t world, uint32_t my_rank,
-                          uint32_t* codes_sorted, void* nodes, void* wide, uint32_t* flags, void* bounds,
-                          const void* scene2x4, int dtype, uint32_t n, void* stream) {
-    if (!gathered || !codes_sorted || !nodes || !wide || !flags || !bounds || !scene2x4 || cap == 0 || world == 0 ||
-        my_rank >= world)
+COL_API size_t col_shard_exchange_bytes(uint32_t span_cap, int dtype) {
+    const size_t off = dtype == COL_F64 ? xchg_span_offset<double>() : xchg_span_offset<float>();
+    return (off + (size_t)span_cap * sizeof(uint32_t) + 15) & ~(size_t)15;
+}
+
+COL_API int col_shard_top_local(const uint32_t* codes_sorted, void* nodes, void* wide, uint32_t* flags, void* bounds,
+                                const void* scene2x4, int dtype, uint32_t n, uint32_t leaf_begin, uint32_t leaf_end,
+                                const void* probe, void* exchange, uint32_t span_cap, void* stream) {
+    if (!codes_sorted || !nodes || !wide || !flags || !bounds || !scene2x4 || !probe || !exchange || span_cap == 0 ||
+        leaf_begin > leaf_end || leaf_end > n)
         return COL_ERR_BAD_ARG;
     if (dtype != COL_F32 && dtype != COL_F64) return COL_ERR_UNSUPPORTED;
     cudaStream_t s = col_stream(stream);
-    const unsigned blocks = col_blocks((uint64_t)cap * world, 256);
-    // (the same values the replicated sort left there; the only ones this rank has after the sharded sort)
+    COL_CUDA(cudaMemsetAsync(exchange, 0, XCHG_HEADER, s));
+    if (leaf_begin == leaf_end) return 0;
+    const uint32_t* items = flags + n;
+    const unsigned blocks = col_blocks(leaf_end - leaf_begin, 256);
     if (dtype == COL_F32)
-        scatter_root_codes_kernel<float><<<blocks, 256, 0, s>>>((const unsigned char*)gathered, cap, world, my_rank, codes_sorted, n);
+        top_local_kernel<float><<<blocks, 256, 0, s>>>(codes_sorted, (col_node*)nodes, (unsigned char*)wide, flags, items,
+                                                       (float*)bounds, (const float*)scene2x4, n, leaf_begin, leaf_end,
+                                                       (const unsigned char*)probe, (unsigned char*)exchange, span_cap);
     else
-        scatter_root_codes_kernel<double><<<blocks, 256, 0, s>>>((const unsigned char*)gathered, cap, world, my_rank, codes_sorted, n);
-    COL_CHECK_LAUNCH();
-    if (dtype == COL_F32)
-        top_packed_kernel<float><<<blocks, 256, 0, s>>>((const unsigned char*)gathered, cap, world, my_rank, codes_sorted,
-                                                        (col_node*)nodes, (unsigned char*)wide, flags, (float*)bounds,
-                                                        (const float*)scene2x4, n);
-    else
-        top_packed_kernel<double><<<blocks, 256, 0, s>>>((const unsigned char*)gathered, cap, world, my_rank, codes_sorted,
-                                                         (col_node*)nodes, (unsigned char*)wide, flags, (double*)bounds,
-                                                         (const double*)scene2x4, n);
+        top_local_kernel<double><<<blocks, 256, 0, s>>>(codes_sorted, (col_node*)nodes, (unsigned char*)wide, flags, items,
+                                                        (double*)bounds, (const double*)scene2x4, n, leaf_begin, leaf_end,
+                                                        (const unsigned char*)probe, (unsigned char*)exchange, span_cap);
     COL_CHECK_LAUNCH();
     return 0;
 }
 
-COL_API int col_shard_halo(const void* gathered, uint32_t cap, uint32_t world, uint32_t my_rank, void* wide, void* bounds,
+COL_API int col_shard_top(const void* gathered, uint32_t span_cap, uint32_t world, uint32_t my_rank,
+                          uint32_t* codes_sorted, void* nodes, void* wide, uint32_t* flags, void* bounds,
+                          const void* scene2x4, int dtype, uint32_t n, const uint64_t* wide_table, void* stream) {
+    if (!gathered || !codes_sorted || !nodes || !wide || !flags || !bounds || !scene2x4 || !wide_table || span_cap == 0 ||
+        world == 0 || my_rank >= world)
+        return COL_ERR_BAD_ARG;
+    if (dtype != COL_F32 && dtype != COL_F64) return COL_ERR_UNSUPPORTED;
+    cudaStream_t s = col_stream(stream);
+    const size_t stride = col_shard_exchange_bytes(span_cap, dtype);
+    const unsigned blocks = col_blocks((uint64_t)XCHG_ROOTS * world, 256);
+    // (the same values the replicated sort left there; the only ones this rank has after the sharded sort)
+    if (dtype == COL_F32) {
+        scatter_root_codes_kernel<float><<<blocks, 256, 0, s>>>((const unsigned char*)gathered, stride, XCHG_ROOTS, world,
+                                                                my_rank, codes_sorted, n);
+        top_packed_kernel<float><<<blocks, 256, 0, s>>>((const unsigned char*)gathered, stride, XCHG_ROOTS, world, my_rank,
+                                                        codes_sorted, (col_node*)nodes, (unsigned char*)wide, flags,
+                                                        (float*)bounds, (const float*)scene2x4, n);
+        fetch_spanning_kernel<float><<<COL_NUM_SMS * 8, 256, 0, s>>>((const unsigned char*)gathered, stride, span_cap, world,
+                                                                     my_rank, (const unsigned long long*)wide_table,
+                                                                     (unsigned char*)wide);
+    } else {
+        scatter_root_codes_kernel<double><<<blocks, 256, 0, s>>>((const unsigned char*)gathered, stride, XCHG_ROOTS, world,
+                                                                 my_rank, codes_sorted, n);
+        top_packed_kernel<double><<<blocks, 256, 0, s>>>((const unsigned char*)gathered, stride, XCHG_ROOTS, world, my_rank,
+                                                         codes_sorted, (col_node*)nodes, (unsigned char*)wide, flags,
+                                                         (double*)bounds, (const double*)scene2x4, n);
+        fetch_spanning_kernel<double><<<COL_NUM_SMS * 8, 256, 0, s>>>((const unsigned char*)gathered, stride, span_cap, world,
+                                                                      my_rank, (const unsigned long long*)wide_table,
+                                                                      (unsigned char*)wide);
+    }
+    COL_CHECK_LAUNCH();
+    return 0;
+}
+
+COL_API int col_shard_halo(const void* probe, uint32_t cap, const void* gathered, uint32_t span_cap, uint32_t world,
+                           uint32_t my_rank, void* wide, void* bounds,
                            const void* scene2x4, int dtype, uint32_t* flags, void* list, uint32_t list_cap,
                            const uint64_t* wide_table, const uint64_t* bounds_table, const uint32_t* win_edges,
                            uint32_t n, uint32_t leaf_begin, uint32_t leaf_end, const uint64_t* ids_table,
                            uint32_t* ids_sorted, void* stream) {
-    if (!gathered || !wide || !bounds || !scene2x4 || !flags || !list || !wide_table || !bounds_table || !win_edges ||
-        cap == 0 || list_cap == 0 || my_rank >= world || (ids_table && !ids_sorted))
+    if (!probe || !gathered || !wide || !bounds || !scene2x4 || !flags || !list || !wide_table || !bounds_table || !win_edges ||
+        cap == 0 || span_cap == 0 || list_cap == 0 || my_rank >= world || (ids_table && !ids_sorted))
         return COL_ERR_BAD_ARG;
     if (dtype != COL_F32 && dtype != COL_F64) return COL_ERR_UNSUPPORTED;
     cudaStream_t s = col_stream(stream);
     COL_CUDA(cudaMemsetAsync(list, 0, 16, s));
     uint32_t* hdr = reinterpret_cast<uint32_t*>(list);
     uint2* entries = reinterpret_cast<uint2*>(reinterpret_cast<unsigned char*>(list) + 16);
-    const size_t stride = col_shard_packed_bytes(cap, dtype);
-    const unsigned char* mine = reinterpret_cast<const unsigned char*>(gathered) + my_rank * stride;
+    const size_t stride = col_shard_exchange_bytes(span_cap, dtype);
+    const unsigned char* mine = reinterpret_cast<const unsigned char*>(probe);
     uint32_t* asked = flags + n;
     const unsigned pblocks = col_blocks(cap, 256);
     if (dtype == COL_F32)
-        halo_probe_kernel<float><<<pblocks, 256, 0, s>>>((const unsigned char*)gathered, world, mine, cap,
+        halo_probe_kernel<float><<<pblocks, 256, 0, s>>>((const unsigned char*)gathered, stride, world, mine, cap,
                                                          (const unsigned char*)wide, (const float*)scene2x4, asked,
                                                          entries, hdr, list_cap, n, leaf_begin, leaf_end);
     else
-        halo_probe_kernel<double><<<pblocks, 256, 0, s>>>((const unsigned char*)gathered, world, mine, cap,
+        halo_probe_kernel<double><<<pblocks, 256, 0, s>>>((const unsigned char*)gathered, stride, world, mine, cap,
                                                           (const unsigned char*)wide, (const double*)scene2x4,
                                                           asked, entries, hdr, list_cap, n, leaf_begin, leaf_end);
     COL_CHECK_LAUNCH();

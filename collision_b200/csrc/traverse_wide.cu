@@ -140,7 +140,13 @@ __device__ __forceinline__ uint32_t walk(const unsigned char* __restrict__ wide,
     int sp = 0;
     stack[sp++] = TRV_DONE;
     uint32_t idx = 0, hits = 0;
+#ifdef COL_DEBUG
+    uint32_t visits = 0;
+#endif
     do {
+#ifdef COL_DEBUG   // a walk over half-built records need not end: trap instead of hanging
+        if (++visits > 2u * leaf_start + 2u || idx >= leaf_start) __trap();
+#endif
         idx = visit<EXACT>(wide, bounds, query, q, leaf_start, idx, stack, sp, [&](uint32_t pos, bool valid) {
             on_leaf(pos, hits, valid);
             hits += valid ? 1u : 0u;

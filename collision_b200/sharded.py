@@ -297,12 +297,15 @@ class ShardedCollider:
         most = max(e - b for b, e in zip(self.edges, self.edges[1:]))
         self._cap = max(1024, most // 16)                    # subtree roots a rank may hand over (typically 1.6 % of its leaves)
         self._list_cap = max(4096, n // 16)                  # remote subtrees a rank may ask for
-        nb = L.col_shard_packed_bytes(self._cap, c.program._code)
-        self._packed = _lib.alloc_bytes(ctx, nb)
+        # the roots the rank's windows hand over: its probe list (stays here)
+        self._packed = _lib.alloc_bytes(ctx, L.col_shard_packed_bytes(self._cap, c.program._code))
+        # what travels: the rank's few range roots + the indices of the spanning nodes it built (as many as roots,
+        # less a few).  After every call that syncs, the exchange is cut down to 1.5 x the most any rank listed
+        # (+ 1024) -- the all-gather moves whole buffers, used or not.  Identical on every rank (derived from the
+        # gathered headers).
+        nb = L.col_shard_exchange_bytes(self._cap, c.program._code)
+        self._xchg = _lib.alloc_bytes(ctx, nb)
         self._gathered = _lib.alloc_bytes(ctx, nb * k)
-        # what actually travels: after every call that syncs, the exchange is cut down to 1.5 x the most roots any
-        # rank handed over (+ 1024) -- the all-gather moves whole buffers, used or not.  Identical on every rank
-        # (derived from the gathered headers).
         self._send_cap = self._cap
         self.sort_count = n           # pairs this rank sorted in the last call that synced
         self._list = _lib.alloc_bytes(ctx, L.col_shard_list_bytes(self._list_cap))
@@ -311,23 +314,24 @@ class ShardedCollider:
         dist.barrier(group=self.group)
 
     def _packed_bytes(self):
-        return _lib.lib().col_shard_packed_bytes(self._send_cap, self.collider.program._code)
+        return _lib.lib().col_shard_exchange_bytes(self._send_cap, self.collider.program._code)
 
     def _check_shard_overflow(self):
         """After a call that synced.  Returns True when the call has to be repeated (the cut-down exchange was
         too small for this frame: it is reset to the full buffers first)."""
         hdr = self._gathered.view(torch.int32)
         stride = self._packed_bytes() // 4
-        heads = torch.stack([hdr[r * stride:r * stride + 2] for r in range(self.world)]).tolist()
-        over_roots = any(h[1] for h in heads)
+        heads = torch.stack([hdr[r * stride:r * stride + 4] for r in range(self.world)]).tolist()
+        over_roots = any(h[1] for h in heads)      # a probe list or the range roots: fixed sizes
+        over_span = any(h[3] for h in heads)
         over_list = bool(int(self._list.view(torch.int32)[1].item()))
-        if over_roots and self._send_cap < self._cap:
+        if over_span and not over_roots and self._send_cap < self._cap:
             self._send_cap = self._cap
             return True
-        if over_roots or over_list:
+        if over_roots or over_span or over_list:
             raise RuntimeError("sharded_build: more subtree roots / remote subtrees than the exchange buffers hold "
                                "(cap {}, list {}); use mode 'gather_inputs' for this scene".format(self._cap, self._list_cap))
-        most = max(h[0] for h in heads)
+        most = max(h[2] for h in heads)
         self._send_cap = min(self._cap, max(self._send_cap if self._send_cap < self._cap else 0, most + most // 2 + 1024))
         if self.sort_mode == "exchange":
             self.sort_count = int(self._plan[8 * self.rank + 1].item())
@@ -536,17 +540,22 @@ class ShardedCollider:
         _lib.check(L.col_shard_build_windows(P(c._codes_bufs[1]), P(leaf_ids), P(c._nodes_buf), P(c._wide_buf),
                                              P(c._flags_buf), P(c._bounds_buf), P(coords_buf), P(radii_buf),
                                              P(c._scene_buf), code, n, self.win_edges[self.rank],
-                                             self.win_edges[self.rank + 1], P(self._packed), self._send_cap, S),
+                                             self.win_edges[self.rank + 1], P(self._packed), self._cap, S),
                    "col_shard_build_windows")
         c._mark(cq, "build_windows", 2)
+        _lib.check(L.col_shard_top_local(P(c._codes_bufs[1]), P(c._nodes_buf), P(c._wide_buf), P(c._flags_buf),
+                                         P(c._bounds_buf), P(c._scene_buf), code, n, self.q_begin, self.q_end,
+                                         P(self._packed), P(self._xchg), self._send_cap, S), "col_shard_top_local")
+        c._mark(cq, "build_top_local", 1)
         nb = self._packed_bytes()
-        dist.all_gather_into_tensor(self._gathered[:nb * self.world], self._packed[:nb], group=self.group)
+        dist.all_gather_into_tensor(self._gathered[:nb * self.world], self._xchg[:nb], group=self.group)
         c._mark(cq, "gather_roots", 0)
         _lib.check(L.col_shard_top(P(self._gathered), self._send_cap, self.world, self.rank, P(c._codes_bufs[1]),
                                    P(c._nodes_buf), P(c._wide_buf), P(c._flags_buf), P(c._bounds_buf),
-                                   P(c._scene_buf), code, n, S), "col_shard_top")
-        c._mark(cq, "build_top", 1)
-        _lib.check(L.col_shard_halo(P(self._gathered), self._send_cap, self.world, self.rank, P(c._wide_buf),
+                                   P(c._scene_buf), code, n, P(self._sb_wide.table), S), "col_shard_top")
+        c._mark(cq, "build_top", 3)
+        _lib.check(L.col_shard_halo(P(self._packed), self._cap, P(self._gathered), self._send_cap, self.world, self.rank,
+                                    P(c._wide_buf),
                                     P(c._bounds_buf), P(c._scene_buf), code, P(c._flags_buf), P(self._list),
                                     self._list_cap, P(self._sb_wide.table), P(self._sb_bounds.table),
                                     P(self._win_edges_dev), n, self.q_begin, self.q_end,

@@ -308,20 +308,29 @@ int col_ipc_close(void* ptr);
  * No reference counterpart.  The windows (256 sorted leaves each) are dealt out to the ranks:
  * col_shard_build_windows  = col_build_refit_wide's window pass for windows [win_begin, win_end) only; the
  *                            subtree roots it hands over are packed into `packed` ({count, overflow} header +
- *                            up to `cap` records {node, lo, hi, box}; col_shard_packed_bytes(cap, dtype) bytes).
- *                            The caller all-gathers the ranks' packed buffers (rank-major) into `gathered`.
- * col_shard_top            = the pass over the nodes that span windows, from the gathered roots of ALL ranks
- *                            (replicated on every rank: it is small).
+ *                            up to `cap` records {node, lo, hi, codes at the ends, box}; col_shard_packed_bytes(cap,
+ *                            dtype) bytes): the rank's PROBE list (it stays on the rank).
+ * col_shard_top_local      = the nodes above the windows that still lie inside the rank's own range of leaves
+ *                            [leaf_begin, leaf_end): climbs from the handed-over roots while the parent stays in
+ *                            range.  Fills `exchange` (col_shard_exchange_bytes(span_cap, dtype) bytes): a header
+ *                            {roots, overflow, spanning nodes, overflow}, the roots of the rank's maximal in-range
+ *                            subtrees (a few dozen) and the indices of the up to span_cap nodes it finished.
+ *                            The caller all-gathers the ranks' exchange buffers (rank-major) into `gathered`.
+ * col_shard_top            = the handful of nodes that span RANKS, from the gathered range roots (on every rank),
+ *                            and the other ranks' spanning records copied from their HBM by the gathered lists
+ *                            (wide_table: the ranks' record arrays as mapped into this process, col_ipc_open).
+ *                            The codes at the other ranks' roots' ends are written into codes_sorted.
  * col_shard_halo           = which in-window subtrees of OTHER ranks can this rank's queries enter (a walk of
- *                            the spanning nodes with each own root's box), and their records + leaf boxes
- *                            copied from the owners' buffers (wide_table / bounds_table: the ranks' base
- *                            addresses as mapped into this process, col_ipc_open) into `wide` / `bounds`.
+ *                            the spanning nodes with each root's box of the probe list), and their records + leaf
+ *                            boxes copied from the owners' buffers (wide_table / bounds_table) into `wide` / `bounds`.
  *                            win_edges: world + 1 window indices (device), rank r owns [win_edges[r], win_edges[r+1]);
  *                            list: col_shard_list_bytes(list_cap) bytes of scratch.  After it the traversal of
  *                            the rank's own queries [leaf_begin, leaf_end) finds everything it touches locally.
  *                            ids_table / ids_sorted (may both be NULL): the sphere ids of the fetched leaves are
  *                            copied from the owners as well (needed after col_shard_sort, see below).
- * Overflow of `cap` / `list_cap` sets word 1 of the respective header (the host checks it when it next syncs).
+ * Overflow of `cap` / span_cap / `list_cap` sets word 1 / 3 of the respective header (the host checks them when it
+ * next syncs); when any rank's exchange overflowed, col_shard_top writes a root that ends every walk at once and the
+ * halo asks for nothing, so that nothing ever walks half-built nodes.
  *
  * col_shard_sort           = the SORT dealt out the same way: positions [pos_lo, pos_hi] of the stable sort of all
  *                            n codes (ids = input positions), written at codes_sorted / ids_sorted + those positions
@@ -339,10 +348,15 @@ int col_shard_build_windows(const uint32_t* codes_sorted, const uint32_t* ids_so
                             uint32_t* flags, void* bounds, const void* coords4, const void* radii,
                             const void* scene2x4, int dtype, uint32_t n, uint32_t win_begin, uint32_t win_end,
                             void* packed, uint32_t cap, void* stream);
-int col_shard_top(const void* gathered, uint32_t cap, uint32_t world, uint32_t my_rank,
+size_t col_shard_exchange_bytes(uint32_t span_cap, int dtype);
+int col_shard_top_local(const uint32_t* codes_sorted, void* nodes, void* wide, uint32_t* flags, void* bounds,
+                        const void* scene2x4, int dtype, uint32_t n, uint32_t leaf_begin, uint32_t leaf_end,
+                        const void* probe, void* exchange, uint32_t span_cap, void* stream);
+int col_shard_top(const void* gathered, uint32_t span_cap, uint32_t world, uint32_t my_rank,
                   uint32_t* codes_sorted, void* nodes, void* wide, uint32_t* flags, void* bounds,
-                  const void* scene2x4, int dtype, uint32_t n, void* stream);
-int col_shard_halo(const void* gathered, uint32_t cap, uint32_t world, uint32_t my_rank, void* wide, void* bounds,
+                  const void* scene2x4, int dtype, uint32_t n, const uint64_t* wide_table, void* stream);
+int col_shard_halo(const void* probe, uint32_t cap, const void* gathered, uint32_t span_cap, uint32_t world,
+                   uint32_t my_rank, void* wide, void* bounds,
                    const void* scene2x4, int dtype, uint32_t* flags, void* list, uint32_t list_cap,
                    const uint64_t* wide_table, const uint64_t* bounds_table, const uint32_t* win_edges,
                    uint32_t n, uint32_t leaf_begin, uint32_t leaf_end, const uint64_t* ids_table,

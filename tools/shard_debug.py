@@ -95,6 +95,8 @@ def main():
     if args.mode == "sharded_build":
         lst = col._list.view(torch.int32)
         print("rank {} root exchange cut to {} of {}".format(rank, col._send_cap, col._cap), flush=True)
+        xh = col._xchg.view(torch.int32)[:4].tolist()
+        print("rank {} range roots {}, spanning nodes listed {} (flags {} {})".format(rank, xh[0], xh[2], xh[1], xh[3]), flush=True)
         print("rank {} roots packed {} of cap {}, remote subtrees fetched {} of {}".format(
             rank, int(col._packed.view(torch.int32)[0].item()), col._cap, int(lst[0].item()), col._list_cap), flush=True)
     col.close()
