@@ -890,7 +890,7 @@ def main():
                     help="override the workload (default: D = configs[3] on one GPU, E = configs[4] on several)")
     ap.add_argument("--n-log2", type=int, default=None, help="override the scene size (development / CI)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
-    ap.add_argument("--shard-sort", default="exchange", choices=["exchange", "local", "replicated"],
+    ap.add_argument("--shard-sort", default=None, choices=["exchange", "local", "replicated"],
                     help="mode sharded_build: how the sort is dealt out (see ShardedCollider)")
     ap.add_argument("--no-stages", action="store_true", help="skip stages_at_target / config_b / weak_b (profiling runs)")
     ap.add_argument("--no-graph", action="store_true", help="enqueue kernel by kernel instead of replaying a CUDA graph")

@@ -4,7 +4,7 @@ N=$1; TAG=${2:-r4x}; SORT=${3:-exchange}; shift 3
 O=gpurun_out; mkdir -p $O
 RUN="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511"
 F=$O/${TAG}_bench_${N}gpu_${SORT}
-timeout 600 $RUN bench.py --gpus $N --steps 20 --warmup 5 --time-n1 --shard-sort $SORT "$@" 2> $F.err | grep -v "^NCCL" | tail -1 > $F.json; echo "bench rc=${PIPESTATUS[0]}"
+timeout 600 $RUN bench.py --gpus $N --steps 20 --warmup 5 --time-n1 $( [ "$SORT" = auto ] || echo --shard-sort $SORT ) "$@" 2> $F.err | grep -v "^NCCL" | tail -1 > $F.json; echo "bench rc=${PIPESTATUS[0]}"
 grep "bench +" $F.err | tail -3
 python - <<PY
 import json

@@ -19,7 +19,7 @@ def main():
     ap.add_argument("--spheres", type=int, default=20011)
     ap.add_argument("--mode", default="sharded_build")
     ap.add_argument("--steps", type=int, default=3)
-    ap.add_argument("--sort", default="exchange", choices=["exchange", "local", "replicated"])
+    ap.add_argument("--sort", default=None, choices=["exchange", "local", "replicated"])
     ap.add_argument("--one-device", action="store_true", help="every rank on cuda:0, gloo for the collectives (cheap multi-rank "
                     "check of the kernels and the peer mappings on a one-GPU box; no graph capture)")
     ap.add_argument("--tiny-send", action="store_true", help="start with a root exchange that is far too small (the call must repeat itself)")
