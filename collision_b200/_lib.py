@@ -68,7 +68,7 @@ SIGNATURES = {
     "col_shard_list_bytes": (_sz, [_u32]),
     "col_shard_build_windows": (_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _int, _u32, _u32, _u32, _vp, _u32, _vp]),
     "col_shard_exchange_bytes": (_sz, [_u32, _int]),
-    "col_shard_top_local": (_int, [_vp, _vp, _vp, _vp, _vp, _vp, _int, _u32, _u32, _u32, _vp, _vp, _u32, _vp]),
+    "col_shard_top_local": (_int, [_vp, _vp, _vp, _vp, _vp, _vp, _int, _u32, _u32, _u32, _vp, _u32, _vp, _u32, _vp]),
     "col_shard_top": (_int, [_vp, _u32, _u32, _u32, _vp, _vp, _vp, _vp, _vp, _vp, _int, _u32, _vp, _vp]),
     "col_shard_halo": (_int, [_vp, _u32, _vp, _u32, _u32, _u32, _vp, _vp, _vp, _int, _vp, _vp, _u32, _vp, _vp, _vp, _u32, _u32,
                               _u32, _vp, _vp, _vp]),

@@ -762,31 +762,30 @@ halo_fetch_kernel(const uint2* __restrict__ list, const uint32_t* __restrict__ l
 template <typename T>
 __global__ void __launch_bounds__(256)
 top_local_kernel(const uint32_t* __restrict__ codes, col_node* __restrict__ nodes, unsigned char* __restrict__ wide,
-                 uint32_t* __restrict__ flags, const uint32_t* __restrict__ items, T* __restrict__ bounds,
+                 uint32_t* __restrict__ flags, T* __restrict__ bounds,
                  const T* __restrict__ scene, uint32_t n, uint32_t leaf_begin, uint32_t leaf_end,
-                 const unsigned char* __restrict__ probe, unsigned char* __restrict__ xchg, uint32_t span_cap) {
-    const uint32_t t = leaf_begin + blockIdx.x * blockDim.x + threadIdx.x;
+                 const unsigned char* __restrict__ probe, uint32_t probe_cap, unsigned char* __restrict__ xchg,
+                 uint32_t span_cap) {
+    // one thread per root of the probe list (dense: one per hand-over SLOT left 98 % of the lanes idle and the
+    // few busy ones spread over 25 x as many warps -- 2.07 ms instead of 0.5 at 2^26 own leaves)
+    const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
     uint32_t* hdr = reinterpret_cast<uint32_t*>(xchg);
+    const uint32_t* probe_hdr = reinterpret_cast<const uint32_t*>(probe);
     // a probe list that overflowed leaves the halo incomplete: everybody has to know (see shard_exchange_overflowed)
-    if (t == leaf_begin && reinterpret_cast<const uint32_t*>(probe)[1]) hdr[1] = 1u;
-    if (t >= leaf_end) return;
-    uint32_t self = items[t];
-    if (self == NO_ARRIVAL) return;
+    if (j == 0 && probe_hdr[1]) hdr[1] = 1u;
+    if (j >= min(probe_hdr[0], probe_cap)) return;
+    const PackedItem<T> root = reinterpret_cast<const PackedItem<T>*>(probe + PACK_HEADER)[j];
+    uint32_t self = root.self;
     const Quant<T> qz = make_quant(scene);
     const uint32_t leaf_start = n - 1;
-    uint32_t lo, hi;
-    if (self >= leaf_start) {
-        lo = hi = self - leaf_start;
-    } else {
-        const uint2 rec = *reinterpret_cast<const uint2*>(nodes + self);   // {lo (window pass), right_edge}
-        lo = rec.x;
-        hi = rec.y;
-    }
-    Box<T> box = load_box_cg(bounds, self);
+    uint32_t lo = root.lo, hi = root.hi;
+    Box<T> box;
+#pragma unroll
+    for (int c = 0; c < 3; c++) { box.lo[c] = root.box[c]; box.hi[c] = root.box[3 + c]; }
     uint3 grid = quantise_box(qz, box.lo, box.hi);
-    uint32_t code_lo = __ldg(codes + lo), code_hi = __ldg(codes + hi);
-    int dl = lo > 0 ? key_delta(lo - 1, __ldg(codes + lo - 1), lo, code_lo) : -1;
-    int dr = hi < leaf_start ? key_delta(hi, code_hi, hi + 1, __ldg(codes + hi + 1)) : -1;
+    uint32_t code_lo = root.code[1], code_hi = root.code[2];
+    int dl = lo > 0 ? key_delta(lo - 1, root.code[0], lo, code_lo) : -1;
+    int dr = hi < leaf_start ? key_delta(hi, code_hi, hi + 1, root.code[3]) : -1;
     const uint32_t code_before = leaf_begin > 0 ? __ldg(codes + leaf_begin - 1) : 0u;
     const uint32_t code_after = leaf_end < n ? __ldg(codes + leaf_end) : 0u;
     uint32_t* span = reinterpret_cast<uint32_t*>(xchg + xchg_span_offset<T>());
@@ -1008,24 +1007,25 @@ COL_API size_t col_shard_exchange_bytes(uint32_t span_cap, int dtype) {
 
 COL_API int col_shard_top_local(const uint32_t* codes_sorted, void* nodes, void* wide, uint32_t* flags, void* bounds,
                                 const void* scene2x4, int dtype, uint32_t n, uint32_t leaf_begin, uint32_t leaf_end,
-                                const void* probe, void* exchange, uint32_t span_cap, void* stream) {
+                                const void* probe, uint32_t probe_cap, void* exchange, uint32_t span_cap, void* stream) {
     if (!codes_sorted || !nodes || !wide || !flags || !bounds || !scene2x4 || !probe || !exchange || span_cap == 0 ||
-        leaf_begin > leaf_end || leaf_end > n)
+        probe_cap == 0 || leaf_begin > leaf_end || leaf_end > n)
         return COL_ERR_BAD_ARG;
     if (dtype != COL_F32 && dtype != COL_F64) return COL_ERR_UNSUPPORTED;
     cudaStream_t s = col_stream(stream);
     COL_CUDA(cudaMemsetAsync(exchange, 0, XCHG_HEADER, s));
     if (leaf_begin == leaf_end) return 0;
-    const uint32_t* items = flags + n;
-    const unsigned blocks = col_blocks(leaf_end - leaf_begin, 256);
+    const unsigned blocks = col_blocks(probe_cap, 256);
     if (dtype == COL_F32)
-        top_local_kernel<float><<<blocks, 256, 0, s>>>(codes_sorted, (col_node*)nodes, (unsigned char*)wide, flags, items,
+        top_local_kernel<float><<<blocks, 256, 0, s>>>(codes_sorted, (col_node*)nodes, (unsigned char*)wide, flags,
                                                        (float*)bounds, (const float*)scene2x4, n, leaf_begin, leaf_end,
-                                                       (const unsigned char*)probe, (unsigned char*)exchange, span_cap);
+                                                       (const unsigned char*)probe, probe_cap, (unsigned char*)exchange,
+                                                       span_cap);
     else
-        top_local_kernel<double><<<blocks, 256, 0, s>>>(codes_sorted, (col_node*)nodes, (unsigned char*)wide, flags, items,
+        top_local_kernel<double><<<blocks, 256, 0, s>>>(codes_sorted, (col_node*)nodes, (unsigned char*)wide, flags,
                                                         (double*)bounds, (const double*)scene2x4, n, leaf_begin, leaf_end,
-                                                        (const unsigned char*)probe, (unsigned char*)exchange, span_cap);
+                                                        (const unsigned char*)probe, probe_cap, (unsigned char*)exchange,
+                                                        span_cap);
     COL_CHECK_LAUNCH();
     return 0;
 }

@@ -548,7 +548,8 @@ class ShardedCollider:
         c._mark(cq, "build_windows", 2)
         _lib.check(L.col_shard_top_local(P(c._codes_bufs[1]), P(c._nodes_buf), P(c._wide_buf), P(c._flags_buf),
                                          P(c._bounds_buf), P(c._scene_buf), code, n, self.q_begin, self.q_end,
-                                         P(self._packed), P(self._xchg), self._send_cap, S), "col_shard_top_local")
+                                         P(self._packed), self._cap, P(self._xchg), self._send_cap, S),
+                   "col_shard_top_local")
         c._mark(cq, "build_top_local", 1)
         nb = self._packed_bytes()
         dist.all_gather_into_tensor(self._gathered[:nb * self.world], self._xchg[:nb], group=self.group)

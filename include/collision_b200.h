@@ -351,7 +351,7 @@ int col_shard_build_windows(const uint32_t* codes_sorted, const uint32_t* ids_so
 size_t col_shard_exchange_bytes(uint32_t span_cap, int dtype);
 int col_shard_top_local(const uint32_t* codes_sorted, void* nodes, void* wide, uint32_t* flags, void* bounds,
                         const void* scene2x4, int dtype, uint32_t n, uint32_t leaf_begin, uint32_t leaf_end,
-                        const void* probe, void* exchange, uint32_t span_cap, void* stream);
+                        const void* probe, uint32_t probe_cap, void* exchange, uint32_t span_cap, void* stream);
 int col_shard_top(const void* gathered, uint32_t span_cap, uint32_t world, uint32_t my_rank,
                   uint32_t* codes_sorted, void* nodes, void* wide, uint32_t* flags, void* bounds,
                   const void* scene2x4, int dtype, uint32_t n, const uint64_t* wide_table, void* stream);
