@@ -723,6 +723,17 @@ halo_fetch_kernel(const uint2* __restrict__ list, const uint32_t* __restrict__ l
                   const unsigned long long* __restrict__ ids_table, const uint32_t* __restrict__ win_edges,
                   uint32_t world, unsigned char* __restrict__ wide, unsigned char* __restrict__ bounds,
                   uint32_t* __restrict__ ids, uint32_t box_bytes, uint32_t n) {
+    if (list_hdr[1]) {
+        // more remote subtrees than the list holds: some would stay unfetched, and a walk into records that were
+        // never written need not end.  Same remedy as in top_packed_kernel: a root that ends every walk of THIS
+        // rank at once (the root is not among the records other ranks copy); the host raises when it next syncs.
+        if (blockIdx.x == 0 && threadIdx.x == 0) {
+            uint4* rp = reinterpret_cast<uint4*>(wide);
+            rp[0] = make_uint4(0x80000000u, 0x80000000u, 0xFFFFFFFFu, 0xFFFFFFFFu);
+            rp[1] = make_uint4(0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu);
+        }
+        return;
+    }
     const uint32_t count = min(list_hdr[0], list_cap);
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t leaf_start = n - 1;
