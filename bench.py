@@ -834,13 +834,15 @@ def run_multi(args):
                          "share_of_step": trav / ms_per_step, "algorithmic_bytes": nbytes,
                          "GBps": nbytes / trav / 1e6, "frac_of_hbm_peak": nbytes / trav / 1e6 / peak,
                          "note": "this rank's 1/{} of the queries".format(world)}
-        dom = max((k for k in stages if k in STAGE_BYTES), key=lambda k: stages[k], default=None)
+        # the largest HBM-bound stage (the traversal and the build are latency-bound: `traversal` above)
+        dom = max((k for k in stages if k in STAGE_BYTES and not k.startswith(("traverse", "tree"))),
+                  key=lambda k: stages[k], default=None)
         roofline = None
         if dom:
-            q = n // world if dom.startswith("traverse") else (R["sort_n"] if dom == "sort" else n)
-            m = R["cap"] if dom.startswith("traverse") else R["total"]
+            q = R["sort_n"] if dom == "sort" else n
+            m = R["total"]
             nbytes = STAGE_BYTES[dom](q, m)
-            roofline = {"kernel": dom, "bound": "latency" if dom.startswith(("traverse", "tree")) else "hbm",
+            roofline = {"kernel": dom, "bound": "hbm",
                         "achieved": nbytes / stages[dom] / 1e6, "peak": peak, "unit": "GB/s",
                         "frac": nbytes / stages[dom] / 1e6 / peak, "traffic": None, "peak_source": peak_src,
                         "algorithmic_bytes": nbytes, "ms": stages[dom], "share_of_step": stages[dom] / ms_per_step}
